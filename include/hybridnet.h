@@ -1,0 +1,189 @@
+/* libhybridnet_sm100.so -- C ABI of the B200 (sm_100a) hot path of the hybrid
+ * segmentation nets (FCT / UNet / AutoEncoder / Autoencoder32K).
+ *
+ * The reference (spygaurad/Transformer-CNN-Hybrid-Network-for-Video-Processing)
+ * has NO FFI: its hot path is `model(x)` / `loss.backward()` over torch.nn
+ * layers (FCT.py:330,337; Model.py:56,58).  Each entry point below replaces the
+ * ATen/cuDNN call behind one of those layers; the reference line it stands in
+ * for is cited beside it.  The host side (package `hybridnet`, Python, because
+ * the reference is Python) binds these with ctypes -- see INTEGRATION.md.
+ *
+ * Conventions
+ *  - every activation is NHWC bf16 in device memory; a tensor is (ptr, ld) where
+ *    ld = elements between consecutive pixels (>= C, multiple of 8, so a channel
+ *    slice of a wider buffer is a tensor too -- that is how concat is free);
+ *  - parameters / parameter gradients are fp32 in the reference's own layout
+ *    (OIHW etc.), i.e. exactly the state_dict tensors;
+ *  - the caller owns all memory; no entry point allocates, synchronises or
+ *    keeps state, so every call is CUDA-graph capturable;
+ *  - `stream` is a cudaStream_t passed as void*;
+ *  - return 0 on success, negative HN_E* otherwise; hn_last_error() gives the
+ *    thread-local message.
+ */
+#ifndef HYBRIDNET_H_
+#define HYBRIDNET_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HN_OK 0
+#define HN_EINVAL (-1)
+#define HN_ECUDA (-2)
+#define HN_EUNSUPPORTED (-3)
+
+enum { HN_ACT_NONE = 0, HN_ACT_RELU = 1, HN_ACT_GELU = 2, HN_ACT_SIGMOID = 3 };
+
+const char* hn_last_error(void);
+int hn_version(void);
+/* device sanity: returns 0 iff the current device is sm_100 */
+int hn_check_device(void);
+
+/* ---- layout (module boundary: x.to(device) FCT.py:326; final mask) ---------- */
+/* [B,C,H,W] fp32 -> [B,H,W,ld] bf16, channels >= C zero-filled up to Cpad */
+int hn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, int W,
+                             int Cpad, int ld, void* stream);
+int hn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int H, int W,
+                             int ld, void* stream);
+/* AvgPool2d(2,2) on NHWC bf16 (FCT.py:238-240 pyramid) */
+int hn_avgpool2_fwd(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldy,
+                    void* stream);
+
+/* ---- convolution as implicit GEMM ----------------------------------------- */
+/* Replaces nn.Conv2d / nn.ConvTranspose2d forward and input-gradient
+ * (FCT.py:88,110-113,140-143,170-172,194-196; UNet.py:19-26,58-61;
+ *  AutoEncoder.py:9-12,36-38,57-59; pyc:AE_32K L24-31,L65-81,L123-150).       */
+typedef struct HnConv {
+  int B, H, W;            /* logical input extent (after the optional x2 upsample) */
+  int C1, C2;             /* channels taken from x1 then x2 (virtual concat); %8==0 */
+  int ld1, ld2;           /* pixel strides of x1 / x2                              */
+  int OH, OW, Cout;       /* output extent and channels (any Cout >= 1)           */
+  int ldy;                /* pixel stride of y                                     */
+  int KH, KW, stride, pad, dil;
+  int mode;               /* 0: ih = oh*stride - pad + kh*dil  (forward conv)
+                             1: ih = (oh + pad - kh*dil)/stride when divisible
+                                (input gradient / transposed conv)                */
+  int ups;                /* 1: x is read through nearest Upsample(x2): x[ih>>1]  */
+  int act;                /* HN_ACT_* applied after bias (+ residual)             */
+  int pshuf;              /* >0: GEMM column n = tap*pshuf + co is stored to pixel
+                             (2*oh + tap/2, 2*ow + tap%2), channel co (ConvT k2s2) */
+  int ldr;                /* pixel stride of residual (if res != NULL)            */
+  int Kpad;               /* row length of packed weights (from hn_conv_kpad)     */
+} HnConv;
+
+int hn_conv_kpad(int KH, int KW, int Cin_pad);   /* packed row length in elements   */
+int hn_conv_npad(int Cout);                      /* packed row count                 */
+/* fp32 parameter -> packed bf16 [Npad][Kpad], k = (kh*KW+kw)*Cpad + c.
+ * element (n,c,kh,kw) is read from src[(n/nmod)*s_nhi + (n%nmod)*s_n + c*s_c + kh*s_kh + kw*s_kw];
+ * c >= Creal or n >= N is written as zero. */
+int hn_pack_weight(const float* src, void* dst, int N, int Creal, int Cpad, int KH, int KW,
+                   long long nmod, long long s_nhi, long long s_n, long long s_c,
+                   long long s_kh, long long s_kw, void* stream);
+/* y = act(conv(x1|x2, w) + bias [+ res]); optional per-channel sum / sum-of-squares
+ * of the stored (bf16-rounded, pre-activation) values for BatchNorm.            */
+int hn_conv2d_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
+                  const float* bias, const void* res, void* y, float* stat_sum,
+                  float* stat_sqsum, void* stream);
+/* dW (fp32, += into a zeroed buffer) for the same HnConv geometry (mode 0 only):
+ * dW[n,c,kh,kw] += sum_p dy[p,n] * x[p@(kh,kw), c], written at
+ * dw[n*s_n + c*s_c + kh*s_kh + kw*s_kw]; c >= Creal skipped.                     */
+int hn_conv2d_wgrad(const HnConv* d, const void* x1, const void* x2, const void* dy,
+                    float* dw, int Creal, long long s_n, long long s_c, long long s_kh,
+                    long long s_kw, void* stream);
+
+/* ---- pointwise / reductions ------------------------------------------------ */
+/* dz = dy * act'(.) (ReLU/sigmoid from the saved output y, GELU from the saved
+ * pre-activation); optional fp32 column sums of dz (bias gradient, += )         */
+int hn_act_bwd(const void* dy, const void* y_or_z, void* dz, long long P, int C, int lddy,
+               int ldy, int lddz, int act, float* dbias, void* stream);
+int hn_colsum(const void* x, long long P, int C, int ld, float* out, void* stream);
+/* y = a + b (+ c) elementwise on [P,C] tensors */
+int hn_add(const void* a, const void* b, const void* c, void* y, long long P, int C, int lda,
+           int ldb, int ldc, int ldy, void* stream);
+/* y = gelu(z1)+gelu(z2)+gelu(z3) (Wide_Focus, FCT.py:118-129) and its backward */
+int hn_gelu3_sum_fwd(const void* z1, const void* z2, const void* z3, void* y, long long n,
+                     void* stream);
+int hn_gelu3_sum_bwd(const void* dy, const void* z1, const void* z2, const void* z3, void* d1,
+                     void* d2, void* d3, long long n, void* stream);
+/* MaxPool2d(2) (FCT.py:147; UNet.py:12) forward / backward (first max wins) */
+int hn_maxpool2_fwd(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldy,
+                    void* stream);
+int hn_maxpool2_bwd(const void* x, const void* dy, void* dx, int B, int H, int W, int C, int ldx,
+                    int lddy, int lddx, void* stream);
+/* gradient of nearest Upsample(x2): dx[h,w] = sum of the 2x2 block of dy */
+int hn_upsample2_bwd(const void* dy, void* dx, int B, int H, int W, int C, int lddy, int lddx,
+                     void* stream);
+/* Dropout / Dropout2d: y = x * keep/(1-p); keep bit = hash(seed, idx) (idx = element,
+ * or (b,c) when channelwise).  The same call with dy gives the backward.        */
+int hn_dropout(const void* x, void* y, int B, long long HW, int C, int ldx, int ldy, float p,
+               unsigned long long seed, int channelwise, void* stream);
+
+/* ---- LayerNorm over C (FCT.py:32-36,89) ------------------------------------- */
+int hn_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, long long P,
+                     int C, int ldx, int ldy, float eps, void* stream);
+/* dx, and += dgamma/dbeta (fp32[C]); recomputes mean/rstd from x */
+int hn_layernorm_bwd(const void* x, const void* dy, void* dx, const float* gamma, float* dgamma,
+                     float* dbeta, long long P, int C, int ldx, int lddy, int lddx, float eps,
+                     void* stream);
+
+/* ---- BatchNorm2d, training and eval (UNet.py:59,62; pyc:AE_32K) ------------- */
+int hn_bn_stats(const void* x, long long P, int C, int ld, float* sum, float* sqsum, void* stream);
+/* mean/rstd from sums; running stats update with momentum and unbiased var      */
+int hn_bn_finalize(const float* sum, const float* sqsum, long long count, int C, float eps,
+                   float momentum, float* mean, float* rstd, float* running_mean,
+                   float* running_var, void* stream);
+/* y = act((x-mean)*rstd*gamma+beta [+ res]) */
+int hn_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd,
+                const float* gamma, const float* beta, long long P, int C, int ldx, int ldr,
+                int ldy, int act, void* stream);
+/* pass 1: dz = dy*act'(y) (written to dz), s1 += sum dz, s2 += sum dz*xhat      */
+int hn_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, const float* mean,
+                     const float* rstd, long long P, int C, int lddy, int ldy, int ldx, int lddz,
+                     int act, float* s1, float* s2, void* stream);
+/* pass 2: dx = gamma*rstd*(dz - s1/P - xhat*s2/P) (training) or gamma*rstd*dz (eval) */
+int hn_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* mean, const float* rstd,
+                    const float* gamma, const float* s1, const float* s2, long long P, int C,
+                    int lddz, int ldx, int lddx, int training, void* stream);
+
+/* ---- conv-projected attention (FCT.py:24-79) -------------------------------- */
+/* q,k,v = LayerNorm_C(ReLU(dwconv3x3(x)+b)) for the three projections in one pass.
+ * w: [3][C][9] fp32, b: [3][C], gamma/beta: [3][C]; out: [3] tensors of [P,C]   */
+int hn_dwconv_relu_ln_fwd(const void* x, void* q, void* k, void* v, const float* w, const float* b,
+                          const float* gamma, const float* beta, int B, int H, int W, int C,
+                          int ldx, int ldo, float eps, void* stream);
+/* backward: dpre[3] (grad at the dwconv output, after LN+ReLU backward), += dgamma/dbeta/db */
+int hn_dwconv_relu_ln_bwd_pre(const void* x, const void* dq, const void* dk, const void* dv,
+                              void* dpre_q, void* dpre_k, void* dpre_v, const float* w,
+                              const float* b, const float* gamma, float* dgamma, float* dbeta,
+                              float* db, int B, int H, int W, int C, int ldx, int ldd, float eps,
+                              void* stream);
+/* dx = sum_t dwconv^T(dpre_t, w_t);  dw[3][C][9] += sum_p dpre_t[p,c] * x[p@tap,c] */
+int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpre_k,
+                              const void* dpre_v, void* dx, const float* w, float* dw, int B, int H,
+                              int W, int C, int ldx, int ldd, int lddx, void* stream);
+/* softmax(Q K^T * scale) V per head, flash style.  q,k,v,o: [B,N,heads*D] with
+ * pixel strides ld*; lse: fp32 [B,heads,N] (log-sum-exp, natural log).
+ * D in {4,8,16,32,64}.  Replaces nn.MultiheadAttention's core (FCT.py:37,75).   */
+int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N,
+                int heads, int D, int ldq, int ldk, int ldv, int ldo, float scale, void* stream);
+int hn_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                const float* lse, float* delta_ws, void* dq, void* dk, void* dv, int B, int N,
+                int heads, int D, int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk,
+                int lddv, float scale, void* stream);
+
+/* ---- tcgen05/TMEM implicit-GEMM convolution (C >= 64 layers) ---------------- */
+/* 3x3 stride-1 conv, Cin%64==0, Cout%64==0, fed by TMA, accumulators in TMEM.   */
+int hn_conv3x3_tc_supported(const HnConv* d);
+int hn_conv3x3_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
+                      const float* bias, void* y, float* stat_sum, float* stat_sqsum,
+                      void* stream);
+
+/* ---- fused multi-tensor AdamW on a flat fp32 arena (FCT.py:305,338) --------- */
+int hn_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                  long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                  int step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HYBRIDNET_H_ */

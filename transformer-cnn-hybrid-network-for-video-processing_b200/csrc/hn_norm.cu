@@ -1,0 +1,305 @@
+// LayerNorm over the channel axis and BatchNorm2d (train/eval) on NHWC bf16.
+// Warp-shuffle reductions across the lanes that share a pixel (LN) and
+// register -> shared -> one-atomic-per-channel column reductions (BN, dgamma).
+#include "hn_common.cuh"
+
+namespace {
+constexpr int TPB = 256;
+inline int grid_for(long long work_items) {
+  long long b = (work_items + TPB - 1) / TPB;
+  long long cap = 148 * 12;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)((b + 2) / 3 * 3);
+}
+__device__ __forceinline__ float group_sum(float v, int CV) {
+  for (int o = 1; o < CV; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// CV = C/8 lanes cooperate on one pixel (CV is a power of two <= 32)
+__global__ void ln_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, const float* __restrict__ gamma,
+                              const float* __restrict__ beta, long long P, int C, int ldx, int ldy, float eps) {
+  const int CV = C / 8;
+  long long total = (P * CV + 31) / 32 * 32;     // keep whole warps alive for the shuffles
+  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int cv = (int)(i0 % CV);
+  float ga[8], be[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { ga[j] = gamma[cv * 8 + j]; be[j] = beta[cv * 8 + j]; }
+  const float invC = 1.f / C;
+  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long pix = i / CV;
+    bool ok = pix < P;
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (ok) load8(x + pix * ldx + cv * 8, f);
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += f[j];
+    float mean = group_sum(s, CV) * invC;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { float d = f[j] - mean; q += d * d; }
+    float rstd = rsqrtf(group_sum(q, CV) * invC + eps);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = (f[j] - mean) * rstd * ga[j] + be[j];
+    if (ok) store8(y + pix * ldy + cv * 8, f);
+  }
+}
+
+__global__ void ln_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ dx,
+                              const float* __restrict__ gamma, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                              long long P, int C, int ldx, int lddy, int lddx, float eps) {
+  extern __shared__ float s_acc[];   // [2][C]
+  const int CV = C / 8;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_acc[i] = 0.f;
+  __syncthreads();
+  long long total = (P * CV + 31) / 32 * 32;
+  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int cv = (int)(i0 % CV);
+  float ga[8], pg[8], pb[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { ga[j] = gamma[cv * 8 + j]; pg[j] = 0.f; pb[j] = 0.f; }
+  const float invC = 1.f / C;
+  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long pix = i / CV;
+    bool ok = pix < P;
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0}, g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (ok) { load8(x + pix * ldx + cv * 8, f); load8(dy + pix * lddy + cv * 8, g); }
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += f[j];
+    float mean = group_sum(s, CV) * invC;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { float d = f[j] - mean; q += d * d; }
+    float rstd = rsqrtf(group_sum(q, CV) * invC + eps);
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float xh = (f[j] - mean) * rstd;
+      float gg = g[j] * ga[j];
+      a += gg; b += gg * xh;
+      pg[j] += g[j] * xh; pb[j] += g[j];
+      f[j] = xh; g[j] = gg;
+    }
+    a = group_sum(a, CV) * invC;
+    b = group_sum(b, CV) * invC;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = rstd * (g[j] - a - f[j] * b);
+    if (ok) store8(dx + pix * lddx + cv * 8, f);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    atomicAdd(&s_acc[cv * 8 + j], pg[j]);
+    atomicAdd(&s_acc[C + cv * 8 + j], pb[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(dgamma + i, s_acc[i]);
+    atomicAdd(dbeta + i, s_acc[C + i]);
+  }
+}
+
+// ---- BatchNorm ----------------------------------------------------------------------
+__global__ void bn_stats_kernel(const bf16* __restrict__ x, long long P, int C, int ld, float* __restrict__ sum,
+                                float* __restrict__ sq) {
+  extern __shared__ float s_acc[];   // [2][C]
+  const int CV = C / 8;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_acc[i] = 0.f;
+  __syncthreads();
+  float ps[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long total = P * CV;
+  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int cv = (int)(i0 % CV);
+  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    load8(x + (i / CV) * ld + cv * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { ps[j] += f[j]; pq[j] += f[j] * f[j]; }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    atomicAdd(&s_acc[cv * 8 + j], ps[j]);
+    atomicAdd(&s_acc[C + cv * 8 + j], pq[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(sum + i, s_acc[i]);
+    atomicAdd(sq + i, s_acc[C + i]);
+  }
+}
+__global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq, long long count, int C,
+                                   float eps, float momentum, float* __restrict__ mean, float* __restrict__ rstd,
+                                   float* __restrict__ rmean, float* __restrict__ rvar) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double m = (double)sum[c] / (double)count;
+  double v = (double)sq[c] / (double)count - m * m;
+  if (v < 0) v = 0;
+  mean[c] = (float)m;
+  rstd[c] = (float)(1.0 / sqrt(v + (double)eps));
+  if (rmean) {
+    double unb = count > 1 ? v * (double)count / (double)(count - 1) : v;
+    rmean[c] = (1.f - momentum) * rmean[c] + momentum * (float)m;
+    rvar[c] = (1.f - momentum) * rvar[c] + momentum * (float)unb;
+  }
+}
+__global__ void bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res, bf16* __restrict__ y,
+                                const float* __restrict__ mean, const float* __restrict__ rstd,
+                                const float* __restrict__ gamma, const float* __restrict__ beta, long long P, int C,
+                                int ldx, int ldr, int ldy, int act) {
+  const int CV = C / 8;
+  long long total = P * CV;
+  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int cv = (int)(i0 % CV);
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    int c = cv * 8 + j;
+    sc[j] = rstd[c] * gamma[c];
+    sh[j] = beta[c] - mean[c] * sc[j];
+  }
+  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long pix = i / CV;
+    float f[8], r[8];
+    load8(x + pix * ldx + cv * 8, f);
+    if (res) load8(res + pix * ldr + cv * 8, r);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = f[j] * sc[j] + sh[j];
+      if (res) v += r[j];
+      f[j] = apply_act(v, act);
+    }
+    store8(y + pix * ldy + cv * 8, f);
+  }
+}
+__global__ void bn_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ x,
+                                     bf16* __restrict__ dz, const float* __restrict__ mean, const float* __restrict__ rstd,
+                                     long long P, int C, int lddy, int ldy, int ldx, int lddz, int act,
+                                     float* __restrict__ s1, float* __restrict__ s2) {
+  extern __shared__ float s_acc[];   // [2][C]
+  const int CV = C / 8;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_acc[i] = 0.f;
+  __syncthreads();
+  long long total = P * CV;
+  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int cv = (int)(i0 % CV);
+  float mu[8], rs[8], p1[8], p2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { mu[j] = mean[cv * 8 + j]; rs[j] = rstd[cv * 8 + j]; p1[j] = p2[j] = 0.f; }
+  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long pix = i / CV;
+    float g[8], a[8], f[8];
+    load8(dy + pix * lddy + cv * 8, g);
+    if (act != HN_ACT_NONE) load8(y + pix * ldy + cv * 8, a);
+    load8(x + pix * ldx + cv * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = g[j];
+      if (act == HN_ACT_RELU) v = a[j] > 0.f ? v : 0.f;
+      else if (act == HN_ACT_SIGMOID) v = v * a[j] * (1.f - a[j]);
+      g[j] = v;
+      float vr = bf16_round(v);
+      p1[j] += vr;
+      p2[j] += vr * (f[j] - mu[j]) * rs[j];
+    }
+    if (dz) store8(dz + pix * lddz + cv * 8, g);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    atomicAdd(&s_acc[cv * 8 + j], p1[j]);
+    atomicAdd(&s_acc[C + cv * 8 + j], p2[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(s1 + i, s_acc[i]);
+    atomicAdd(s2 + i, s_acc[C + i]);
+  }
+}
+__global__ void bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, bf16* __restrict__ dx,
+                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                    const float* __restrict__ gamma, const float* __restrict__ s1,
+                                    const float* __restrict__ s2, long long P, int C, int lddz, int ldx, int lddx,
+                                    int training) {
+  const int CV = C / 8;
+  long long total = P * CV;
+  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int cv = (int)(i0 % CV);
+  float mu[8], rs[8], k[8], m1[8], m2[8];
+  const float invP = 1.f / (float)P;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    int c = cv * 8 + j;
+    mu[j] = mean[c]; rs[j] = rstd[c]; k[j] = gamma[c] * rstd[c];
+    m1[j] = training ? s1[c] * invP : 0.f;
+    m2[j] = training ? s2[c] * invP : 0.f;
+  }
+  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long pix = i / CV;
+    float g[8], f[8];
+    load8(dz + pix * lddz + cv * 8, g);
+    load8(x + pix * ldx + cv * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float xh = (f[j] - mu[j]) * rs[j];
+      f[j] = k[j] * (g[j] - m1[j] - xh * m2[j]);
+    }
+    store8(dx + pix * lddx + cv * 8, f);
+  }
+}
+}  // namespace
+
+#define ST ((cudaStream_t)stream)
+#define REQ_CV(C, name) HN_REQUIRE((C) > 0 && (C) % 8 == 0 && (768 % ((C) / 8)) == 0 && (C) <= 2048, name ": unsupported channel count %d", (C))
+#define REQ_LN(C, name) HN_REQUIRE((C) >= 8 && (C) <= 256 && ((C) & ((C)-1)) == 0, name ": C must be a power of two in [8,256], got %d", (C))
+
+extern "C" int hn_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, long long P, int C, int ldx, int ldy, float eps, void* stream) {
+  REQ_LN(C, "layernorm_fwd");
+  HN_REQUIRE(x && y && gamma && beta, "layernorm_fwd: null");
+  ln_fwd_kernel<<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (bf16*)y, gamma, beta, P, C, ldx, ldy, eps);
+  HN_CHECK_LAUNCH("ln_fwd");
+  return HN_OK;
+}
+extern "C" int hn_layernorm_bwd(const void* x, const void* dy, void* dx, const float* gamma, float* dgamma, float* dbeta, long long P, int C, int ldx, int lddy, int lddx, float eps, void* stream) {
+  REQ_LN(C, "layernorm_bwd");
+  HN_REQUIRE(x && dy && dx && gamma && dgamma && dbeta, "layernorm_bwd: null");
+  ln_bwd_kernel<<<grid_for(P * (C / 8)), TPB, 2 * C * sizeof(float), ST>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx, gamma, dgamma, dbeta, P, C, ldx, lddy, lddx, eps);
+  HN_CHECK_LAUNCH("ln_bwd");
+  return HN_OK;
+}
+extern "C" int hn_bn_stats(const void* x, long long P, int C, int ld, float* sum, float* sqsum, void* stream) {
+  REQ_CV(C, "bn_stats");
+  HN_REQUIRE(x && sum && sqsum, "bn_stats: null");
+  bn_stats_kernel<<<grid_for(P * (C / 8)), TPB, 2 * C * sizeof(float), ST>>>((const bf16*)x, P, C, ld, sum, sqsum);
+  HN_CHECK_LAUNCH("bn_stats");
+  return HN_OK;
+}
+extern "C" int hn_bn_finalize(const float* sum, const float* sqsum, long long count, int C, float eps, float momentum, float* mean, float* rstd, float* running_mean, float* running_var, void* stream) {
+  HN_REQUIRE(sum && sqsum && mean && rstd && count > 0 && C > 0, "bn_finalize: bad args");
+  HN_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_finalize: running stats come in pairs");
+  bn_finalize_kernel<<<hn_cdiv(C, 128), 128, 0, ST>>>(sum, sqsum, count, C, eps, momentum, mean, rstd, running_mean, running_var);
+  HN_CHECK_LAUNCH("bn_finalize");
+  return HN_OK;
+}
+extern "C" int hn_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd, const float* gamma, const float* beta, long long P, int C, int ldx, int ldr, int ldy, int act, void* stream) {
+  REQ_CV(C, "bn_apply");
+  HN_REQUIRE(x && y && mean && rstd && gamma && beta, "bn_apply: null");
+  bn_apply_kernel<<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (const bf16*)res, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act);
+  HN_CHECK_LAUNCH("bn_apply");
+  return HN_OK;
+}
+extern "C" int hn_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, const float* mean, const float* rstd, long long P, int C, int lddy, int ldy, int ldx, int lddz, int act, float* s1, float* s2, void* stream) {
+  REQ_CV(C, "bn_bwd_reduce");
+  HN_REQUIRE(dy && x && mean && rstd && s1 && s2 && (act == HN_ACT_NONE || y), "bn_bwd_reduce: null");
+  bn_bwd_reduce_kernel<<<grid_for(P * (C / 8)), TPB, 2 * C * sizeof(float), ST>>>((const bf16*)dy, (const bf16*)y, (const bf16*)x, (bf16*)dz, mean, rstd, P, C, lddy, ldy, ldx, lddz, act, s1, s2);
+  HN_CHECK_LAUNCH("bn_bwd_reduce");
+  return HN_OK;
+}
+extern "C" int hn_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* mean, const float* rstd, const float* gamma, const float* s1, const float* s2, long long P, int C, int lddz, int ldx, int lddx, int training, void* stream) {
+  REQ_CV(C, "bn_bwd_apply");
+  HN_REQUIRE(dz && x && dx && mean && rstd && gamma && s1 && s2, "bn_bwd_apply: null");
+  bn_bwd_apply_kernel<<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)dz, (const bf16*)x, (bf16*)dx, mean, rstd, gamma, s1, s2, P, C, lddz, ldx, lddx, training);
+  HN_CHECK_LAUNCH("bn_bwd_apply");
+  return HN_OK;
+}
