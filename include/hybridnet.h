@@ -96,6 +96,8 @@ int hn_conv2d_wgrad(const HnConv* d, const void* x1, const void* x2, const void*
  * pre-activation); optional fp32 column sums of dz (bias gradient, += )         */
 int hn_act_bwd(const void* dy, const void* y_or_z, void* dz, long long P, int C, int lddy,
                int ldy, int lddz, int act, float* dbias, void* stream);
+/* y = act(x) (GELU after a conv whose pre-activation must be kept for backward) */
+int hn_act_fwd(const void* x, void* y, long long P, int C, int ldx, int ldy, int act, void* stream);
 int hn_colsum(const void* x, long long P, int C, int ld, float* out, void* stream);
 /* y = a + b (+ c) elementwise on [P,C] tensors */
 int hn_add(const void* a, const void* b, const void* c, void* y, long long P, int C, int lda,

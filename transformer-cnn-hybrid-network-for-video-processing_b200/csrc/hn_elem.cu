@@ -186,6 +186,18 @@ __global__ void act_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restri
     for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(dbias + i, s_acc[i]);
   }
 }
+__global__ void act_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, long long P, int CV, int ldx, int ldy, int act) {
+  long long total = P * CV;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long pix = i / CV;
+    int cv = (int)(i - pix * CV);
+    float f[8];
+    load8(x + pix * ldx + cv * 8, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = apply_act(f[j], act);
+    store8(y + pix * ldy + cv * 8, f);
+  }
+}
 __global__ void colsum_kernel(const bf16* __restrict__ x, long long P, int C, int ld, float* __restrict__ out) {
   extern __shared__ float s_acc[];
   const int CV = C / 8;
@@ -357,5 +369,12 @@ extern "C" int hn_dropout(const void* x, void* y, int B, long long HW, int C, in
   HN_REQUIRE(x && y && p >= 0.f && p < 1.f, "dropout: bad args");
   dropout_kernel<<<grid_for((long long)B * HW * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (bf16*)y, B, HW, C, ldx, ldy, p, seed, channelwise);
   HN_CHECK_LAUNCH("dropout");
+  return HN_OK;
+}
+extern "C" int hn_act_fwd(const void* x, void* y, long long P, int C, int ldx, int ldy, int act, void* stream) {
+  REQ_C8(C, "act_fwd");
+  HN_REQUIRE(x && y, "act_fwd: null");
+  act_fwd_kernel<<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (bf16*)y, P, C / 8, ldx, ldy, act);
+  HN_CHECK_LAUNCH("act_fwd");
   return HN_OK;
 }

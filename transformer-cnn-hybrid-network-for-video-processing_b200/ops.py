@@ -1,0 +1,745 @@
+"""Autograd-visible operators of the hot path: every forward/backward below is a
+call into libhybridnet_sm100.so (no ATen compute kernels; torch only allocates
+device memory and tracks the autograd graph).
+
+Activations are NHWC bf16 tensors ``[B,H,W,Cp]`` with unit channel stride, where
+Cp is the channel count rounded up to 8 (only the RGB input and the 1/3-channel
+heads are actually padded).  A channel slice ``t[..., a:b]`` of such a tensor is
+itself a valid operand (pixel stride = ld), which is how concat costs nothing.
+"""
+import math
+import weakref
+
+import torch
+
+from . import _lib
+from ._lib import ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID, HnConv, call
+
+ACTS = {"none": ACT_NONE, None: ACT_NONE, "relu": ACT_RELU, "gelu": ACT_GELU, "sigmoid": ACT_SIGMOID}
+
+
+def pad8(c):
+    return (c + 7) // 8 * 8
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _nhwc_ok(t):
+    if t.dtype != torch.bfloat16 or t.dim() != 4 or not t.is_cuda:
+        return False
+    B, H, W, C = t.shape
+    ld = t.stride(2) if W > 1 else None
+    if t.stride(3) != 1 and C > 1:
+        return False
+    if ld is None:
+        ld = t.stride(1) if H > 1 else (t.stride(0) if B > 1 else C)
+        if ld % 8 or ld < C:
+            return False
+        return (H == 1 or t.stride(1) == W * ld) and (B == 1 or t.stride(0) == H * W * ld)
+    if ld % 8 or ld < C:
+        return False
+    if H > 1 and t.stride(1) != W * ld:
+        return False
+    if B > 1 and t.stride(0) != H * W * ld:
+        return False
+    return t.data_ptr() % 16 == 0
+
+
+def nhwc(t):
+    """Return (tensor, ld) with the tensor in a layout the kernels accept."""
+    if not _nhwc_ok(t):
+        t = t.contiguous()
+        if not _nhwc_ok(t):
+            raise RuntimeError(f"hybridnet: expected NHWC bf16 CUDA tensor with C%8==0, got {t.dtype} {tuple(t.shape)}")
+    B, H, W, C = t.shape
+    if W > 1:
+        ld = t.stride(2)
+    elif H > 1:
+        ld = t.stride(1)
+    elif B > 1:
+        ld = t.stride(0)
+    else:
+        ld = C
+    return t, ld
+
+
+def _new(B, H, W, C, like, zero=False):
+    f = torch.zeros if zero else torch.empty
+    return f((B, H, W, C), dtype=torch.bfloat16, device=like.device)
+
+
+def _f32(n, like, zero=True):
+    f = torch.zeros if zero else torch.empty
+    return f(n, dtype=torch.float32, device=like.device)
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+# ----------------------------------------------------------------------------
+# layout at the module boundary
+# ----------------------------------------------------------------------------
+class _ToNHWC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = x.contiguous().float()
+        B, C, H, W = x.shape
+        ctx.C = C
+        y = _new(B, H, W, pad8(C), x)
+        call("hn_nchw_f32_to_nhwc_bf16", x.data_ptr(), y.data_ptr(), B, C, H, W, pad8(C), pad8(C), _stream())
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy, ld = nhwc(dy)
+        B, H, W, _ = dy.shape
+        dx = torch.empty((B, ctx.C, H, W), dtype=torch.float32, device=dy.device)
+        call("hn_nhwc_bf16_to_nchw_f32", dy.data_ptr(), dx.data_ptr(), B, ctx.C, H, W, ld, _stream())
+        return dx
+
+
+class _ToNCHW(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, C):
+        x, ld = nhwc(x)
+        B, H, W, Cp = x.shape
+        ctx.Cp = Cp
+        y = torch.empty((B, C, H, W), dtype=torch.float32, device=x.device)
+        call("hn_nhwc_bf16_to_nchw_f32", x.data_ptr(), y.data_ptr(), B, C, H, W, ld, _stream())
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous().float()
+        B, C, H, W = dy.shape
+        dx = _new(B, H, W, ctx.Cp, dy)
+        call("hn_nchw_f32_to_nhwc_bf16", dy.data_ptr(), dx.data_ptr(), B, C, H, W, ctx.Cp, ctx.Cp, _stream())
+        return dx, None
+
+
+def to_nhwc(x):
+    """[B,C,H,W] fp32 -> [B,H,W,pad8(C)] bf16 (x.to(device) boundary, FCT.py:326)."""
+    return _ToNHWC.apply(x)
+
+
+def to_nchw(x, C):
+    return _ToNCHW.apply(x, C)
+
+
+def avgpool2(x):
+    """AvgPool2d(2,2) of the input pyramid (FCT.py:238-240); the RGB frames carry no grad."""
+    x, ld = nhwc(x.detach())
+    B, H, W, C = x.shape
+    y = _new(B, H // 2, W // 2, C, x)
+    call("hn_avgpool2_fwd", x.data_ptr(), y.data_ptr(), B, H, W, C, ld, C, _stream())
+    return y
+
+
+# ----------------------------------------------------------------------------
+# packed-weight cache (derived bf16 copies; the fp32 Parameter stays the truth)
+# ----------------------------------------------------------------------------
+_pack_cache = weakref.WeakKeyDictionary()
+
+
+def _packed(w, kind, Cpad):
+    """kind: 'fwd'  conv OIHW as [Cout][(kh,kw,ci)]
+             'dgrad' conv OIHW as [Cin][(kh,kw,co)]          (input gradient)
+             'tfwd' convT IOHW(k2) as [(tap,co)][ci]          (1x1 GEMM + pixel shuffle)
+             'tdgrad' convT IOHW as [Cin][(kh,kw,co)]         (k2 s2 conv of dy)"""
+    owner = w._base if w._base is not None else w
+    key = (kind, Cpad, w.storage_offset(), tuple(w.shape))
+    ent = _pack_cache.get(owner)
+    ver = (owner._version, owner.data_ptr())
+    if ent is None or ent.get("ver") != ver:
+        ent = {"ver": ver}
+        _pack_cache[owner] = ent
+    if key in ent:
+        return ent[key]
+    src = w.detach()
+    assert src.dtype == torch.float32 and src.is_contiguous()
+    d0, d1, KH, KW = src.shape
+    big = 1 << 40
+    if kind == "fwd":
+        N, Creal, kh, kw = d0, d1, KH, KW
+        args = (big, 0, d1 * KH * KW, KH * KW, KW, 1)
+    elif kind == "dgrad":
+        N, Creal, kh, kw = d1, d0, KH, KW
+        args = (big, 0, KH * KW, d1 * KH * KW, KW, 1)
+    elif kind == "tfwd":        # weight [Cin, Cout, 2, 2]; n = tap*Cout + co ; c = ci
+        N, Creal, kh, kw = 4 * d1, d0, 1, 1
+        args = (d1, 1, 4, d1 * 4, 0, 0)
+    elif kind == "tdgrad":      # n = ci, c = co, taps (kh,kw)
+        N, Creal, kh, kw = d0, d1, KH, KW
+        args = (big, 0, d1 * KH * KW, KH * KW, KW, 1)
+    else:
+        raise KeyError(kind)
+    lib = _lib.load()
+    Kpad = lib.hn_conv_kpad(kh, kw, Cpad)
+    Npad = lib.hn_conv_npad(N)
+    buf = torch.empty((Npad, Kpad), dtype=torch.bfloat16, device=w.device)
+    call("hn_pack_weight", src.data_ptr(), buf.data_ptr(), N, Creal, Cpad, kh, kw, *args, _stream())
+    ent[key] = (buf, Kpad)
+    return ent[key]
+
+
+def _desc(**kw):
+    d = HnConv()
+    for k, v in kw.items():
+        setattr(d, k, int(v))
+    return d
+
+
+def _conv_raw(x1, x2, wp, Kpad, bias, res, *, OH, OW, Cout, KH, KW, stride, pad, dil, mode=0, ups=0,
+              act=ACT_NONE, pshuf=0, stats=None, out=None, H=None, W=None):
+    """One hn_conv2d_fwd launch.  x1/x2 already validated NHWC."""
+    x1, ld1 = nhwc(x1)
+    B = x1.shape[0]
+    H = H if H is not None else x1.shape[1] << ups
+    W = W if W is not None else x1.shape[2] << ups
+    C1 = x1.shape[3]
+    C2, ld2 = 0, 0
+    if x2 is not None:
+        x2, ld2 = nhwc(x2)
+        C2 = x2.shape[3]
+    if out is None:
+        oc = pad8(pshuf if pshuf else Cout)
+        oh, ow = (2 * OH, 2 * OW) if pshuf else (OH, OW)
+        out = _new(B, oh, ow, oc, x1, zero=(oc != (pshuf if pshuf else Cout)))
+    out_t, ldy = nhwc(out)
+    assert out_t.data_ptr() == out.data_ptr()
+    ldr = 0
+    if res is not None:
+        res, ldr = nhwc(res)
+    d = _desc(B=B, H=H, W=W, C1=C1, C2=C2, ld1=ld1, ld2=ld2, OH=OH, OW=OW, Cout=Cout, ldy=ldy, KH=KH, KW=KW,
+              stride=stride, pad=pad, dil=dil, mode=mode, ups=ups, act=act, pshuf=pshuf, ldr=ldr, Kpad=Kpad)
+    s0 = s1 = None
+    if stats is not None:
+        s0, s1 = stats
+    call("hn_conv2d_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), _ptr(res), out.data_ptr(),
+         _ptr(s0), _ptr(s1), _stream())
+    return out
+
+
+def _wgrad_raw(x1, x2, dz, dw, *, Creal, OH, OW, Cout, KH, KW, stride, pad, dil, ups, strides, H=None, W=None):
+    x1, ld1 = nhwc(x1)
+    B = x1.shape[0]
+    H = H if H is not None else x1.shape[1] << ups
+    W = W if W is not None else x1.shape[2] << ups
+    C2, ld2 = 0, 0
+    if x2 is not None:
+        x2, ld2 = nhwc(x2)
+        C2 = x2.shape[3]
+    dz, lddz = nhwc(dz)
+    lib = _lib.load()
+    d = _desc(B=B, H=H, W=W, C1=x1.shape[3], C2=C2, ld1=ld1, ld2=ld2, OH=OH, OW=OW, Cout=Cout, ldy=lddz, KH=KH,
+              KW=KW, stride=stride, pad=pad, dil=dil, mode=0, ups=ups, act=0, pshuf=0, ldr=0,
+              Kpad=lib.hn_conv_kpad(KH, KW, x1.shape[3] + C2))
+    call("hn_conv2d_wgrad", d, x1.data_ptr(), _ptr(x2), dz.data_ptr(), dw.data_ptr(), Creal, *strides, _stream())
+
+
+# ----------------------------------------------------------------------------
+# convolution (+bias +residual +activation), optionally followed by BatchNorm
+# ----------------------------------------------------------------------------
+def _act_bwd(dy, yz, act, want_dbias):
+    """dz = dy * act'(.) ; dbias = column sums of dz (fp32[Cp])."""
+    dy, lddy = nhwc(dy)
+    B, H, W, C = dy.shape
+    P = B * H * W
+    dbias = _f32(C, dy) if want_dbias else None
+    if act == ACT_NONE:
+        if want_dbias:
+            call("hn_colsum", dy.data_ptr(), P, C, lddy, dbias.data_ptr(), _stream())
+        return dy, dbias
+    yz, ldy = nhwc(yz)
+    dz = _new(B, H, W, C, dy)
+    call("hn_act_bwd", dy.data_ptr(), yz.data_ptr(), dz.data_ptr(), P, C, lddy, ldy, C, act, _ptr(dbias), _stream())
+    return dz, dbias
+
+
+class _Geom:
+    """Static geometry of one conv layer call (kept on ctx for backward)."""
+    __slots__ = ("KH", "KW", "stride", "pad", "dil", "ups", "transposed", "Cin", "Cout", "H", "W", "OH", "OW")
+
+
+def _geom(x1, x2, weight, stride, pad, dil, ups, transposed):
+    g = _Geom()
+    g.transposed = transposed
+    g.stride, g.pad, g.dil, g.ups = stride, pad, dil, ups
+    g.KH, g.KW = weight.shape[2], weight.shape[3]
+    g.H, g.W = x1.shape[1] << ups, x1.shape[2] << ups
+    if transposed:
+        assert g.KH == 2 and g.KW == 2 and stride == 2 and pad == 0 and x2 is None and not ups
+        g.Cin, g.Cout = weight.shape[0], weight.shape[1]
+        g.OH, g.OW = g.H, g.W           # GEMM runs on the input grid; output is 2x
+    else:
+        g.Cout, g.Cin = weight.shape[0], weight.shape[1]
+        g.OH = (g.H + 2 * pad - dil * (g.KH - 1) - 1) // stride + 1
+        g.OW = (g.W + 2 * pad - dil * (g.KW - 1) - 1) // stride + 1
+    return g
+
+
+def _conv_forward(g, x1, x2, weight, bias, res, act, stats=None):
+    Cp = x1.shape[3] + (x2.shape[3] if x2 is not None else 0)
+    if g.transposed:
+        wp, Kpad = _packed(weight, "tfwd", Cp)
+        return _conv_raw(x1, None, wp, Kpad, bias, res, OH=g.OH, OW=g.OW, Cout=g.Cout, KH=1, KW=1, stride=1, pad=0,
+                         dil=1, act=act, pshuf=g.Cout, stats=stats)
+    wp, Kpad = _packed(weight, "fwd", Cp)
+    return _conv_raw(x1, x2, wp, Kpad, bias, res, OH=g.OH, OW=g.OW, Cout=g.Cout, KH=g.KH, KW=g.KW, stride=g.stride,
+                     pad=g.pad, dil=g.dil, ups=g.ups, act=act, stats=stats)
+
+
+def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
+    """dz: gradient at the conv output (NHWC, padded channels zero). Returns dx1, dx2, dW."""
+    dx1 = dx2 = dw = None
+    dz, _ = nhwc(dz)
+    B = x1.shape[0]
+    C1 = x1.shape[3]
+    C2 = x2.shape[3] if x2 is not None else 0
+    if need_dw:
+        dw = torch.zeros_like(weight, dtype=torch.float32)
+        if g.transposed:
+            # dW[ci][co][kh][kw] = sum_p x[p,ci] * dy[2p+(kh,kw), co]: wgrad of the k2s2 conv dy -> x
+            _wgrad_raw(dz, None, x1, dw, Creal=g.Cout, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
+                       dil=1, ups=0, strides=(g.Cout * 4, 4, 2, 1))
+        else:
+            _wgrad_raw(x1, x2, dz, dw, Creal=g.Cin, OH=g.OH, OW=g.OW, Cout=g.Cout, KH=g.KH, KW=g.KW,
+                       stride=g.stride, pad=g.pad, dil=g.dil, ups=g.ups,
+                       strides=(g.Cin * g.KH * g.KW, g.KH * g.KW, g.KW, 1), H=g.H, W=g.W)
+    if need_dx:
+        if g.transposed:
+            wp, Kpad = _packed(weight, "tdgrad", dz.shape[3])
+            dx1 = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
+                            dil=1)
+        else:
+            wp, Kpad = _packed(weight, "dgrad", dz.shape[3])
+            full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=g.KH, KW=g.KW,
+                             stride=g.stride, pad=g.pad, dil=g.dil, mode=1, H=g.OH, W=g.OW)
+            if full.shape[3] != C1 + C2:        # image input: Cin=3 padded to 8
+                assert C2 == 0 and full.shape[3] == C1
+            if g.ups:
+                small = _new(B, g.H // 2, g.W // 2, full.shape[3], full)
+                call("hn_upsample2_bwd", full.data_ptr(), small.data_ptr(), B, g.H // 2, g.W // 2, full.shape[3],
+                     full.shape[3], full.shape[3], _stream())
+                full = small
+            dx1 = full[..., :C1] if C2 else full
+            dx2 = full[..., C1:] if C2 else None
+    return dx1, dx2, dw
+
+
+class _ConvFn(torch.autograd.Function):
+    """y = act(conv(x1|x2) + bias [+ res])  -- nn.Conv2d / nn.ConvTranspose2d forward+backward."""
+
+    @staticmethod
+    def forward(ctx, x1, x2, weight, bias, res, stride, pad, dil, ups, act, transposed):
+        x1, _ = nhwc(x1)
+        if x2 is not None:
+            x2, _ = nhwc(x2)
+        g = _geom(x1, x2, weight, stride, pad, dil, ups, transposed)
+        y = _conv_forward(g, x1, x2, weight, bias, res, act)
+        ctx.g, ctx.act = g, act
+        ctx.has_bias, ctx.has_res = bias is not None, res is not None
+        ctx.save_for_backward(x1, x2, weight, y if act != ACT_NONE else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x1, x2, weight, y = ctx.saved_tensors
+        g = ctx.g
+        need = ctx.needs_input_grad
+        dz, dbias = _act_bwd(dy, y, ctx.act, ctx.has_bias and need[3])
+        dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2])
+        if dbias is not None:
+            dbias = dbias[: g.Cout]
+        return (dx1 if need[0] else None, dx2 if need[1] else None, dw, dbias,
+                dz if (ctx.has_res and need[4]) else None, None, None, None, None, None, None)
+
+
+class _ActFn(torch.autograd.Function):
+    """Stand-alone activation that keeps its input (GELU needs the pre-activation in backward)."""
+
+    @staticmethod
+    def forward(ctx, z, act):
+        z, ld = nhwc(z)
+        B, H, W, C = z.shape
+        y = _new(B, H, W, C, z)
+        call("hn_act_fwd", z.data_ptr(), y.data_ptr(), B * H * W, C, ld, C, act, _stream())
+        ctx.act = act
+        ctx.save_for_backward(z)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (z,) = ctx.saved_tensors
+        dz, _ = _act_bwd(dy, z, ctx.act, False)
+        return dz, None
+
+
+def conv2d(x, weight, bias=None, *, x2=None, res=None, stride=1, pad=1, dil=1, ups=0, act="none", transposed=False):
+    a = ACTS[act]
+    if a == ACT_GELU:      # GELU' needs z: keep the pre-activation, apply GELU as its own pass
+        z = _ConvFn.apply(x, x2, weight, bias, res, stride, pad, dil, ups, ACT_NONE, transposed)
+        return _ActFn.apply(z, ACT_GELU)
+    return _ConvFn.apply(x, x2, weight, bias, res, stride, pad, dil, ups, a, transposed)
+
+
+def _pad_vec(v, n, fill=0.0):
+    if v.numel() == n:
+        return v.detach().float().contiguous()
+    out = torch.full((n,), fill, dtype=torch.float32, device=v.device)
+    out[: v.numel()] = v.detach()
+    return out
+
+
+class _BnActFn(torch.autograd.Function):
+    """y = act(BatchNorm2d(z) [+ res]) with batch statistics in training mode.
+    If stats=(sum,sqsum) is given they came for free from the producing conv's epilogue."""
+
+    @staticmethod
+    def forward(ctx, z, gamma, beta, res, running_mean, running_var, training, momentum, eps, act, stats, count_real):
+        z, ldz = nhwc(z)
+        B, H, W, Cp = z.shape
+        P = B * H * W
+        C = gamma.numel()
+        gam, bet = _pad_vec(gamma, Cp), _pad_vec(beta, Cp)
+        mean, rstd = _f32(Cp, z, False), _f32(Cp, z, False)
+        if training:
+            if stats is None:
+                s0, s1 = _f32(Cp, z), _f32(Cp, z)
+                call("hn_bn_stats", z.data_ptr(), P, Cp, ldz, s0.data_ptr(), s1.data_ptr(), _stream())
+            else:
+                s0, s1 = stats
+            rm = rv = None
+            if running_mean is not None:
+                rm, rv = _pad_vec(running_mean, Cp), _pad_vec(running_var, Cp, 1.0)
+            call("hn_bn_finalize", s0.data_ptr(), s1.data_ptr(), P, Cp, eps, momentum, mean.data_ptr(),
+                 rstd.data_ptr(), _ptr(rm), _ptr(rv), _stream())
+            if rm is not None:
+                running_mean.copy_(rm[:C])
+                running_var.copy_(rv[:C])
+        else:
+            mean = _pad_vec(running_mean, Cp)
+            rstd = torch.rsqrt(_pad_vec(running_var, Cp, 1.0) + eps)
+        y = _new(B, H, W, Cp, z)
+        ldr = 0
+        if res is not None:
+            res, ldr = nhwc(res)
+        call("hn_bn_apply", z.data_ptr(), _ptr(res), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gam.data_ptr(),
+             bet.data_ptr(), P, Cp, ldz, ldr, Cp, act, _stream())
+        ctx.act, ctx.training, ctx.C, ctx.has_res = act, training, C, res is not None
+        ctx.save_for_backward(z, y if act != ACT_NONE else None, mean, rstd, gam)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        z, y, mean, rstd, gam = ctx.saved_tensors
+        dy, lddy = nhwc(dy)
+        z, ldz = nhwc(z)
+        B, H, W, Cp = z.shape
+        P = B * H * W
+        s1, s2 = _f32(Cp, z), _f32(Cp, z)
+        need_dz_buf = ctx.act != ACT_NONE
+        dz = _new(B, H, W, Cp, z) if need_dz_buf else dy
+        lddz = Cp if need_dz_buf else lddy
+        ldy = 0
+        if y is not None:
+            y, ldy = nhwc(y)
+        call("hn_bn_bwd_reduce", dy.data_ptr(), _ptr(y), z.data_ptr(), dz.data_ptr() if need_dz_buf else 0,
+             mean.data_ptr(), rstd.data_ptr(), P, Cp, lddy, ldy, ldz, lddz, ctx.act, s1.data_ptr(), s2.data_ptr(),
+             _stream())
+        dx = _new(B, H, W, Cp, z)
+        call("hn_bn_bwd_apply", dz.data_ptr(), z.data_ptr(), dx.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+             gam.data_ptr(), s1.data_ptr(), s2.data_ptr(), P, Cp, lddz, ldz, Cp, 1 if ctx.training else 0, _stream())
+        C = ctx.C
+        return (dx, s2[:C].clone(), s1[:C].clone(), dz if ctx.has_res else None,
+                None, None, None, None, None, None, None, None)
+
+
+def bn_act(z, gamma, beta, running_mean, running_var, training, *, res=None, momentum=0.1, eps=1e-5, act="none",
+           stats=None):
+    return _BnActFn.apply(z, gamma, beta, res, running_mean, running_var, training, momentum, eps, ACTS[act], stats,
+                          None)
+
+
+class _ConvStatsFn(torch.autograd.Function):
+    """conv (+bias) whose epilogue also emits the per-channel sum / sum-of-squares BatchNorm needs."""
+
+    @staticmethod
+    def forward(ctx, x1, x2, weight, bias, stride, pad, dil, ups, transposed):
+        x1, _ = nhwc(x1)
+        if x2 is not None:
+            x2, _ = nhwc(x2)
+        g = _geom(x1, x2, weight, stride, pad, dil, ups, transposed)
+        Cp = pad8(g.Cout)
+        s0, s1 = _f32(Cp, x1), _f32(Cp, x1)
+        y = _conv_forward(g, x1, x2, weight, bias, None, ACT_NONE, stats=(s0, s1))
+        ctx.g, ctx.has_bias = g, bias is not None
+        ctx.save_for_backward(x1, x2, weight)
+        ctx.mark_non_differentiable(s0, s1)
+        return y, s0, s1
+
+    @staticmethod
+    def backward(ctx, dy, _a, _b):
+        x1, x2, weight = ctx.saved_tensors
+        g = ctx.g
+        need = ctx.needs_input_grad
+        dz, dbias = _act_bwd(dy, None, ACT_NONE, ctx.has_bias and need[3])
+        dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2])
+        if dbias is not None:
+            dbias = dbias[: g.Cout]
+        return (dx1 if need[0] else None, dx2 if need[1] else None, dw, dbias, None, None, None, None, None)
+
+
+def conv_bn_act(x, weight, bias, bn, *, x2=None, res=None, stride=1, pad=1, dil=1, ups=0, act="relu",
+                transposed=False):
+    """Conv2d/ConvTranspose2d -> BatchNorm2d -> activation (UNet.py:54-66; pyc:AE_32K).  In training
+    the batch statistics ride the conv epilogue; ``bn`` is the BatchNorm2d module (params + buffers)."""
+    training = bn.training or (bn.running_mean is None)
+    if training:
+        z, s0, s1 = _ConvStatsFn.apply(x, x2, weight, bias, stride, pad, dil, ups, transposed)
+        stats = (s0, s1)
+        if bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+    else:
+        z = conv2d(x, weight, bias, x2=x2, stride=stride, pad=pad, dil=dil, ups=ups, transposed=transposed)
+        stats = None
+    return bn_act(z, bn.weight, bn.bias, bn.running_mean, bn.running_var, training, res=res, momentum=bn.momentum,
+                  eps=bn.eps, act=act, stats=stats)
+
+
+# ----------------------------------------------------------------------------
+# pooling / dropout / pointwise
+# ----------------------------------------------------------------------------
+class _MaxPool2Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x, ld = nhwc(x)
+        B, H, W, C = x.shape
+        y = _new(B, H // 2, W // 2, C, x)
+        call("hn_maxpool2_fwd", x.data_ptr(), y.data_ptr(), B, H, W, C, ld, C, _stream())
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        x, ld = nhwc(x)
+        dy, lddy = nhwc(dy)
+        B, H, W, C = x.shape
+        dx = _new(B, H, W, C, x)
+        call("hn_maxpool2_bwd", x.data_ptr(), dy.data_ptr(), dx.data_ptr(), B, H, W, C, ld, lddy, C, _stream())
+        return dx
+
+
+def maxpool2(x):
+    """nn.MaxPool2d(2) (FCT.py:147; UNet.py:12)."""
+    return _MaxPool2Fn.apply(x)
+
+
+_dropout_seed = [0x5DEECE66D]
+
+
+def manual_seed(seed):
+    """Seed of the stateless dropout hash (per-rank under data parallelism)."""
+    _dropout_seed[0] = int(seed) & ((1 << 62) - 1)
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, channelwise, seed):
+        x, ld = nhwc(x)
+        B, H, W, C = x.shape
+        y = _new(B, H, W, C, x)
+        call("hn_dropout", x.data_ptr(), y.data_ptr(), B, H * W, C, ld, C, p, seed, int(channelwise), _stream())
+        ctx.p, ctx.cw, ctx.seed = p, channelwise, seed
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy, ld = nhwc(dy)
+        B, H, W, C = dy.shape
+        dx = _new(B, H, W, C, dy)
+        call("hn_dropout", dy.data_ptr(), dx.data_ptr(), B, H * W, C, ld, C, ctx.p, ctx.seed, int(ctx.cw), _stream())
+        return dx, None, None, None
+
+
+class _MaskMulFn(torch.autograd.Function):
+    """Injected dropout mask (parity tests): y = x * mask, mask already scaled by 1/(1-p)."""
+
+    @staticmethod
+    def forward(ctx, x, mask):
+        ctx.save_for_backward(mask)
+        return x * mask
+
+    @staticmethod
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        return dy * mask, None
+
+
+def dropout(x, p, training, channelwise=False, mask=None):
+    """nn.Dropout / nn.Dropout2d.  ``mask`` (NHWC bf16, pre-scaled) overrides the hash for parity tests."""
+    if mask is not None:
+        return _MaskMulFn.apply(x, mask)
+    if not training or p == 0.0:
+        return x
+    _dropout_seed[0] = (_dropout_seed[0] * 6364136223846793005 + 1442695040888963407) & ((1 << 62) - 1)
+    return _DropoutFn.apply(x, float(p), channelwise, _dropout_seed[0])
+
+
+class _AddFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        a, lda = nhwc(a)
+        b, ldb = nhwc(b)
+        B, H, W, C = a.shape
+        y = _new(B, H, W, C, a)
+        call("hn_add", a.data_ptr(), b.data_ptr(), 0, y.data_ptr(), B * H * W, C, lda, ldb, 0, C, _stream())
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        return dy, dy
+
+
+def add(a, b):
+    """torch.add residual (FCT.py:96,101)."""
+    return _AddFn.apply(a, b)
+
+
+class _Gelu3SumFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, z1, z2, z3):
+        z1, z2, z3 = z1.contiguous(), z2.contiguous(), z3.contiguous()
+        y = torch.empty_like(z1)
+        call("hn_gelu3_sum_fwd", z1.data_ptr(), z2.data_ptr(), z3.data_ptr(), y.data_ptr(), z1.numel(), _stream())
+        ctx.save_for_backward(z1, z2, z3)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        z1, z2, z3 = ctx.saved_tensors
+        dy = dy.contiguous()
+        d1, d2, d3 = torch.empty_like(z1), torch.empty_like(z1), torch.empty_like(z1)
+        call("hn_gelu3_sum_bwd", dy.data_ptr(), z1.data_ptr(), z2.data_ptr(), z3.data_ptr(), d1.data_ptr(),
+             d2.data_ptr(), d3.data_ptr(), z1.numel(), _stream())
+        return d1, d2, d3
+
+
+def gelu3_sum(z1, z2, z3):
+    """gelu(z1)+gelu(z2)+gelu(z3): the three Wide_Focus branches (FCT.py:118-129)."""
+    return _Gelu3SumFn.apply(z1, z2, z3)
+
+
+class _LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        x, ld = nhwc(x)
+        B, H, W, C = x.shape
+        y = _new(B, H, W, C, x)
+        call("hn_layernorm_fwd", x.data_ptr(), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), B * H * W, C, ld, C,
+             eps, _stream())
+        ctx.eps = eps
+        ctx.save_for_backward(x, gamma)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma = ctx.saved_tensors
+        x, ld = nhwc(x)
+        dy, lddy = nhwc(dy)
+        B, H, W, C = x.shape
+        dx = _new(B, H, W, C, x)
+        dg, db = _f32(C, x), _f32(C, x)
+        call("hn_layernorm_bwd", x.data_ptr(), dy.data_ptr(), dx.data_ptr(), gamma.data_ptr(), dg.data_ptr(),
+             db.data_ptr(), B * H * W, C, ld, lddy, C, ctx.eps, _stream())
+        return dx, dg, db, None
+
+
+def layernorm_c(x, gamma, beta, eps=1e-5):
+    """nn.LayerNorm(C) applied on the channel axis (FCT.py:97-99)."""
+    return _LayerNormFn.apply(x, gamma, beta, eps)
+
+
+# ----------------------------------------------------------------------------
+# conv-projected attention (FCT.py:24-79)
+# ----------------------------------------------------------------------------
+class _DwLnQKVFn(torch.autograd.Function):
+    """q,k,v = LayerNorm_C(ReLU(depthwise3x3(x))) for the three projections, one pass over x."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, gamma, beta, eps):
+        # w [3,C,9], b/gamma/beta [3,C] fp32 (stacked from conv_{q,k,v} / layernorm_{q,k,v})
+        x, ld = nhwc(x)
+        B, H, W, C = x.shape
+        qkv = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=x.device)
+        call("hn_dwconv_relu_ln_fwd", x.data_ptr(), qkv[0].data_ptr(), qkv[1].data_ptr(), qkv[2].data_ptr(),
+             w.data_ptr(), b.data_ptr(), gamma.data_ptr(), beta.data_ptr(), B, H, W, C, ld, C, eps, _stream())
+        ctx.eps = eps
+        ctx.save_for_backward(x, w, b, gamma)
+        return qkv[0], qkv[1], qkv[2]
+
+    @staticmethod
+    def backward(ctx, dq, dk, dv):
+        x, w, b, gamma = ctx.saved_tensors
+        x, ld = nhwc(x)
+        B, H, W, C = x.shape
+        dq, dk, dv = dq.contiguous(), dk.contiguous(), dv.contiguous()
+        dpre = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=x.device)
+        dgam, dbet, dbias = _f32((3, C), x), _f32((3, C), x), _f32((3, C), x)
+        call("hn_dwconv_relu_ln_bwd_pre", x.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+             dpre[0].data_ptr(), dpre[1].data_ptr(), dpre[2].data_ptr(), w.data_ptr(), b.data_ptr(), gamma.data_ptr(),
+             dgam.data_ptr(), dbet.data_ptr(), dbias.data_ptr(), B, H, W, C, ld, C, ctx.eps, _stream())
+        dx = _new(B, H, W, C, x)
+        dw = _f32((3, C, 9), x)
+        call("hn_dwconv_bwd_data_weight", x.data_ptr(), dpre[0].data_ptr(), dpre[1].data_ptr(), dpre[2].data_ptr(),
+             dx.data_ptr(), w.data_ptr(), dw.data_ptr(), B, H, W, C, ld, C, C, _stream())
+        return dx, dw, dbias, dgam, dbet, None
+
+
+def dwconv_relu_ln_qkv(x, w, b, gamma, beta, eps=1e-5):
+    return _DwLnQKVFn.apply(x, w, b, gamma, beta, eps)
+
+
+class _AttnFn(torch.autograd.Function):
+    """softmax(Q K^T / sqrt(d)) V per head, flash style; q,k,v: [B,H,W,heads*d] (N = H*W tokens)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, heads):
+        q, ldq = nhwc(q)
+        k, ldk = nhwc(k)
+        v, ldv = nhwc(v)
+        B, H, W, C = q.shape
+        N, D = H * W, C // heads
+        scale = 1.0 / math.sqrt(D)
+        o = _new(B, H, W, C, q)
+        lse = torch.empty((B, heads, N), dtype=torch.float32, device=q.device)
+        call("hn_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D,
+             ldq, ldk, ldv, C, scale, _stream())
+        ctx.heads, ctx.scale = heads, scale
+        ctx.save_for_backward(q, k, v, o, lse)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        q, ldq = nhwc(q)
+        k, ldk = nhwc(k)
+        v, ldv = nhwc(v)
+        do, lddo = nhwc(do)
+        B, H, W, C = q.shape
+        heads = ctx.heads
+        N, D = H * W, C // heads
+        dqkv = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=q.device)
+        delta = torch.empty((B, heads, N), dtype=torch.float32, device=q.device)
+        call("hn_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(),
+             delta.data_ptr(), dqkv[0].data_ptr(), dqkv[1].data_ptr(), dqkv[2].data_ptr(), B, N, heads, D, ldq, ldk,
+             ldv, C, lddo, C, C, C, ctx.scale, _stream())
+        return dqkv[0], dqkv[1], dqkv[2], None
+
+
+def attention(q, k, v, heads):
+    return _AttnFn.apply(q, k, v, heads)
