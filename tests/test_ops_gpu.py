@@ -1,0 +1,339 @@
+"""Per-operator parity: every CUDA kernel (through the C ABI, via hybridnet.ops) against the
+same op in plain PyTorch fp32.  Operands are pre-rounded to bf16 so the comparison measures
+the kernel's fp32 accumulation + one bf16 output rounding.
+Tolerances: forward rel-L2 <= 4e-3 (SURVEY 8(c) per-conv bound), gradients rel-L2 <= 1e-2.
+"""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from tests.util import bf16r, nchw_f32, nhwc_bf16, rel_l2
+
+pytestmark = pytest.mark.gpu
+FWD_TOL, BWD_TOL = 4e-3, 1e-2
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import hybridnet
+    from hybridnet import _lib
+    _lib.call("hn_check_device")
+    return hybridnet.ops
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _rand(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return bf16r((torch.rand(*shape, generator=g) * 2 - 1) * scale).to(_dev())
+
+
+def test_layout_roundtrip(ops):
+    x = _rand(2, 3, 16, 24, seed=1)
+    y = ops.to_nhwc(x)
+    assert y.shape == (2, 16, 24, 8) and y.dtype == torch.bfloat16
+    assert torch.equal(y[..., 3:], torch.zeros_like(y[..., 3:]))
+    assert torch.equal(ops.to_nchw(y, 3), x)
+    assert torch.equal(y, nhwc_bf16(x))
+
+
+CONV_CASES = [
+    # Cin, Cout, k, stride, pad, dil, H, act, bias
+    (3, 8, 3, 1, 1, 1, 32, "relu", True),        # FCT block_1.conv1_a (RGB padded to 8)
+    (8, 8, 3, 1, 1, 1, 32, "relu", True),
+    (16, 16, 3, 1, 2, 2, 16, "none", True),      # Wide_Focus conv2 (dilation 2)
+    (32, 32, 3, 1, 3, 3, 16, "none", True),      # Wide_Focus conv3 (dilation 3)
+    (8, 1, 3, 1, 1, 1, 32, "sigmoid", True),     # DS_out conv3
+    (8, 3, 3, 1, 1, 1, 16, "relu", True),        # AutoEncoder head
+    (64, 128, 3, 1, 1, 1, 16, "none", False),    # UNet level 3
+    (128, 64, 3, 1, 1, 1, 8, "relu", True),
+    (3, 64, 7, 2, 3, 1, 32, "none", False),      # Encoder_32K conv1
+    (64, 64, 3, 2, 1, 1, 16, "none", False),     # Bottleneck conv2 stride 2
+    (64, 256, 1, 1, 0, 1, 16, "none", False),    # Bottleneck 1x1
+    (256, 512, 1, 2, 0, 1, 16, "none", False),   # downsample 1x1 stride 2
+    (192, 64, 3, 1, 1, 1, 16, "none", True),     # Decoder_32K conv5
+    (32, 1, 1, 1, 0, 1, 16, "sigmoid", True),    # UNet head 1x1
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv2d_fwd_bwd(ops, case):
+    Cin, Cout, k, stride, pad, dil, H, act, has_bias = case
+    B = 2
+    x = _rand(B, Cin, H, H, seed=2).requires_grad_(True)
+    w = _rand(Cout, Cin, k, k, seed=3, scale=1.0 / math.sqrt(Cin * k * k)).requires_grad_(True)
+    b = _rand(Cout, seed=4, scale=0.1).requires_grad_(True) if has_bias else None
+    ref = F.conv2d(x, w, b, stride, pad, dil)
+    ref = {"relu": F.relu, "sigmoid": torch.sigmoid, "none": lambda t: t}[act](ref)
+    gy = _rand(*ref.shape, seed=5)
+    ref.backward(gy)
+    xr, wr, br = x.grad.clone(), w.grad.clone(), (b.grad.clone() if has_bias else None)
+    x.grad = w.grad = None
+    if has_bias:
+        b.grad = None
+
+    xn = ops.to_nhwc(x)
+    y = ops.conv2d(xn, w, b, stride=stride, pad=pad, dil=dil, act=act)
+    out = ops.to_nchw(y, Cout)
+    assert out.shape == ref.shape
+    assert rel_l2(out, ref) < FWD_TOL
+    out.backward(gy)
+    assert rel_l2(x.grad, xr) < BWD_TOL
+    assert rel_l2(w.grad, wr) < BWD_TOL
+    if has_bias:
+        assert rel_l2(b.grad, br) < BWD_TOL
+
+
+def test_conv_virtual_concat_upsample_residual(ops):
+    """cat([a,b]) folded into the K loop; nearest-x2 upsample folded into the gather; residual epilogue."""
+    B, H = 2, 16
+    a = _rand(B, 16, H, H, seed=1).requires_grad_(True)
+    b2 = _rand(B, 16, H, H, seed=2).requires_grad_(True)
+    w = _rand(16, 32, 3, 3, seed=3, scale=0.06).requires_grad_(True)
+    bias = _rand(16, seed=4, scale=0.1).requires_grad_(True)
+    res = _rand(B, 16, H, H, seed=6).requires_grad_(True)
+    ref = F.conv2d(torch.cat([a, b2], 1), w, bias, 1, 1) + res
+    gy = _rand(*ref.shape, seed=5)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (a, b2, w, bias, res)]
+    for t in (a, b2, w, bias, res):
+        t.grad = None
+    y = ops.conv2d(ops.to_nhwc(a), w, bias, x2=ops.to_nhwc(b2), res=ops.to_nhwc(res))
+    out = ops.to_nchw(y, 16)
+    assert rel_l2(out, ref) < FWD_TOL
+    out.backward(gy)
+    for t, r in zip((a, b2, w, bias, res), want):
+        assert rel_l2(t.grad, r) < BWD_TOL
+
+    s = _rand(B, 8, H // 2, H // 2, seed=7).requires_grad_(True)
+    w2 = _rand(8, 8, 3, 3, seed=8, scale=0.1).requires_grad_(True)
+    ref = F.relu(F.conv2d(F.interpolate(s, scale_factor=2.0, mode="nearest"), w2, None, 1, 1))
+    gy = _rand(*ref.shape, seed=9)
+    ref.backward(gy)
+    sr, wr = s.grad.clone(), w2.grad.clone()
+    s.grad = w2.grad = None
+    out = ops.to_nchw(ops.conv2d(ops.to_nhwc(s), w2, None, ups=1, act="relu"), 8)
+    assert rel_l2(out, ref) < FWD_TOL
+    out.backward(gy)
+    assert rel_l2(s.grad, sr) < BWD_TOL and rel_l2(w2.grad, wr) < BWD_TOL
+
+
+@pytest.mark.parametrize("cin,cout", [(64, 32), (512, 256), (256, 384)])
+def test_conv_transpose_k2s2(ops, cin, cout):
+    B, H = 2, 8
+    x = _rand(B, cin, H, H, seed=1).requires_grad_(True)
+    w = _rand(cin, cout, 2, 2, seed=2, scale=1.0 / math.sqrt(cin)).requires_grad_(True)
+    b = _rand(cout, seed=3, scale=0.1).requires_grad_(True)
+    ref = F.conv_transpose2d(x, w, b, stride=2)
+    gy = _rand(*ref.shape, seed=4)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (x, w, b)]
+    for t in (x, w, b):
+        t.grad = None
+    out = ops.to_nchw(ops.conv2d(ops.to_nhwc(x), w, b, stride=2, pad=0, transposed=True), cout)
+    assert out.shape == ref.shape
+    assert rel_l2(out, ref) < FWD_TOL
+    out.backward(gy)
+    for t, r in zip((x, w, b), want):
+        assert rel_l2(t.grad, r) < BWD_TOL
+
+
+@pytest.mark.parametrize("C,training,act,with_res", [(32, True, "relu", False), (256, True, "relu", True),
+                                                      (192, True, "relu", False), (64, False, "relu", False),
+                                                      (1, True, "sigmoid", False), (3, True, "relu", False)])
+def test_conv_bn_act(ops, C, training, act, with_res):
+    import torch.nn as nn
+    B, H, Cin = 4, 8, 16
+    x = _rand(B, Cin, H, H, seed=1).requires_grad_(True)
+    w = _rand(C, Cin, 3, 3, seed=2, scale=0.1).requires_grad_(True)
+    res = _rand(B, C, H, H, seed=8).requires_grad_(True) if with_res else None
+    bn_ref, bn = nn.BatchNorm2d(C).to(_dev()), nn.BatchNorm2d(C).to(_dev())
+    with torch.no_grad():
+        for m in (bn_ref, bn):
+            m.weight.copy_(_rand(C, seed=3) * 0.5 + 1.0)
+            m.bias.copy_(_rand(C, seed=4) * 0.3)
+            m.running_mean.copy_(_rand(C, seed=5) * 0.1)
+            m.running_var.copy_(_rand(C, seed=6).abs() + 0.5)
+    bn_ref.train(training)
+    bn.train(training)
+    z = bn_ref(F.conv2d(x, w, None, 1, 1))
+    if with_res:
+        z = z + res
+    ref = torch.sigmoid(z) if act == "sigmoid" else F.relu(z)
+    gy = _rand(*ref.shape, seed=7)
+    ref.backward(gy)
+    want = [x.grad.clone(), w.grad.clone(), bn_ref.weight.grad.clone(), bn_ref.bias.grad.clone()]
+    res_want = res.grad.clone() if with_res else None
+    x.grad = w.grad = None
+    if with_res:
+        res.grad = None
+    y = ops.conv_bn_act(ops.to_nhwc(x), w, None, bn, res=ops.to_nhwc(res) if with_res else None, act=act)
+    out = ops.to_nchw(y, C)
+    assert rel_l2(out, ref) < 6e-3
+    out.backward(gy)
+    got = [x.grad, w.grad, bn.weight.grad, bn.bias.grad]
+    for g, r in zip(got, want):
+        assert rel_l2(g, r) < 2e-2
+    if with_res:
+        assert rel_l2(res.grad, res_want) < BWD_TOL
+    if training:
+        assert torch.allclose(bn.running_mean, bn_ref.running_mean, atol=2e-3)
+        assert torch.allclose(bn.running_var, bn_ref.running_var, rtol=1e-2, atol=1e-3)
+        assert int(bn.num_batches_tracked) == 1
+
+
+def test_maxpool_dropout_add_gelu3_layernorm(ops):
+    B, C, H = 2, 16, 16
+    x = _rand(B, C, H, H, seed=1).requires_grad_(True)
+    ref = F.max_pool2d(x, 2)
+    gy = _rand(*ref.shape, seed=2)
+    ref.backward(gy)
+    xr = x.grad.clone()
+    x.grad = None
+    out = ops.to_nchw(ops.maxpool2(ops.to_nhwc(x)), C)
+    assert torch.equal(out, ref)
+    out.backward(gy)
+    assert torch.equal(x.grad, xr)
+
+    # ties (post-ReLU zeros): the first maximum in scan order takes the gradient, as in PyTorch
+    xt = torch.zeros(1, 8, 4, 4, device=_dev()).requires_grad_(True)
+    F.max_pool2d(xt, 2).sum().backward()
+    want = xt.grad.clone()
+    xt.grad = None
+    ops.to_nchw(ops.maxpool2(ops.to_nhwc(xt)), 8).sum().backward()
+    assert torch.equal(xt.grad, want)
+
+    # dropout: keep-rate, scaling, and backward uses the same mask
+    xn = ops.to_nhwc(torch.ones(4, 8, 64, 64, device=_dev())).requires_grad_(True)
+    ops.manual_seed(123)
+    y = ops.dropout(xn, 0.3, True)
+    keep = (y > 0).float().mean().item()
+    assert abs(keep - 0.7) < 0.01
+    assert torch.allclose(y[y > 0].float(), torch.tensor(1 / 0.7, device=_dev()), rtol=1e-2)
+    y.sum().backward()
+    assert torch.equal((xn.grad > 0), (y > 0))
+    y2 = ops.dropout(xn.detach(), 0.3, True, channelwise=True)      # Dropout2d: whole (b,c) planes
+    plane = (y2 > 0).float().mean(dim=(1, 2))
+    assert torch.all((plane == 0) | (plane == 1))
+    assert ops.dropout(xn, 0.3, False) is xn
+
+    a = _rand(B, C, H, H, seed=3).requires_grad_(True)
+    b = _rand(B, C, H, H, seed=4).requires_grad_(True)
+    out = ops.to_nchw(ops.add(ops.to_nhwc(a), ops.to_nhwc(b)), C)
+    assert rel_l2(out, a + b) < FWD_TOL
+
+    zs = [_rand(B, C, H, H, seed=s).requires_grad_(True) for s in (5, 6, 7)]
+    ref = sum(F.gelu(z) for z in zs)
+    gy = _rand(*ref.shape, seed=8)
+    ref.backward(gy)
+    want = [z.grad.clone() for z in zs]
+    for z in zs:
+        z.grad = None
+    out = ops.to_nchw(ops.gelu3_sum(*[ops.to_nhwc(z) for z in zs]), C)
+    assert rel_l2(out, ref) < 6e-3
+    out.backward(gy)
+    for z, r in zip(zs, want):
+        assert rel_l2(z.grad, r) < BWD_TOL
+
+    for Cc in (8, 16, 32, 64, 128):
+        x = _rand(B, Cc, 8, 8, seed=9).requires_grad_(True)
+        g = (_rand(Cc, seed=10) * 0.5 + 1).requires_grad_(True)
+        be = (_rand(Cc, seed=11) * 0.2).requires_grad_(True)
+        ref = F.layer_norm(x.permute(0, 2, 3, 1), (Cc,), g, be, 1e-5).permute(0, 3, 1, 2)
+        gy = _rand(*ref.shape, seed=12)
+        ref.backward(gy)
+        want = [t.grad.clone() for t in (x, g, be)]
+        for t in (x, g, be):
+            t.grad = None
+        out = ops.to_nchw(ops.layernorm_c(ops.to_nhwc(x), g, be), Cc)
+        assert rel_l2(out, ref) < FWD_TOL
+        out.backward(gy)
+        for t, r in zip((x, g, be), want):
+            assert rel_l2(t.grad, r) < BWD_TOL
+
+
+@pytest.mark.parametrize("C", [8, 16, 32, 64, 128])
+def test_dwconv_relu_ln_qkv(ops, C):
+    B, H = 2, 12
+    x = _rand(B, C, H, H, seed=1).requires_grad_(True)
+    w = _rand(3, C, 9, seed=2, scale=0.4).requires_grad_(True)
+    b = _rand(3, C, seed=3, scale=0.2).requires_grad_(True)
+    g = (_rand(3, C, seed=4) * 0.5 + 1).requires_grad_(True)
+    be = (_rand(3, C, seed=5) * 0.2).requires_grad_(True)
+    refs = []
+    for t in range(3):
+        y = F.relu(F.conv2d(x, w[t].view(C, 1, 3, 3), b[t], 1, 1, 1, C))
+        refs.append(F.layer_norm(y.permute(0, 2, 3, 1), (C,), g[t], be[t], 1e-5).permute(0, 3, 1, 2))
+    gys = [_rand(*refs[0].shape, seed=6 + t) for t in range(3)]
+    torch.autograd.backward(refs, gys)
+    want = [t.grad.clone() for t in (x, w, b, g, be)]
+    for t in (x, w, b, g, be):
+        t.grad = None
+    outs = ops.dwconv_relu_ln_qkv(ops.to_nhwc(x), w, b, g, be)
+    outs = [ops.to_nchw(o, C) for o in outs]
+    for o, r in zip(outs, refs):
+        assert rel_l2(o, r) < FWD_TOL
+    torch.autograd.backward(outs, gys)
+    for t, r in zip((x, w, b, g, be), want):
+        assert rel_l2(t.grad, r) < 1.5e-2
+
+
+@pytest.mark.parametrize("D,N", [(4, 256), (4, 100), (8, 256), (16, 192), (32, 64), (64, 64), (64, 4), (8, 1024)])
+def test_flash_attention(ops, D, N):
+    """softmax(QK^T/sqrt(d))V, heads=2, incl. ragged N (not a multiple of the 64-token tile)."""
+    B, heads = 2, 2
+    C = heads * D
+    q, k, v = [_rand(B, N, C, seed=s, scale=1.5).requires_grad_(True) for s in (1, 2, 3)]
+
+    def split(t):
+        return t.view(B, N, heads, D).transpose(1, 2)
+    s = split(q) @ split(k).transpose(-1, -2) / math.sqrt(D)
+    ref = (torch.softmax(s, -1) @ split(v)).transpose(1, 2).reshape(B, N, C)
+    gy = _rand(B, N, C, seed=4)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (q, k, v)]
+    for t in (q, k, v):
+        t.grad = None
+
+    class _Cast(torch.autograd.Function):          # fp32 [B,N,C] <-> bf16 [B,1,N,C] (test glue)
+        @staticmethod
+        def forward(ctx, t):
+            return t.to(torch.bfloat16).view(B, 1, N, C)
+
+        @staticmethod
+        def backward(ctx, g):
+            return g.float().view(B, N, C)
+    o = ops.attention(_Cast.apply(q), _Cast.apply(k), _Cast.apply(v), heads)
+    out = o.float().view(B, N, C)
+    assert rel_l2(out, ref) < 6e-3
+    out.backward(gy)
+    for t, r in zip((q, k, v), want):
+        assert rel_l2(t.grad, r) < 1.5e-2
+
+
+def test_adamw_matches_torch(ops):
+    from hybridnet import _lib
+    n = 10007
+    p = _rand(n, seed=1).float().contiguous()
+    g = _rand(n, seed=2).float().contiguous()
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([ref], lr=1e-3)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for step in (1, 2, 3):
+        ref.grad = g.clone()
+        opt.step()
+        _lib.call("hn_adamw_step", p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), n, 1e-3, 0.9, 0.999, 1e-8,
+                  1e-2, step, 1.0, torch.cuda.current_stream().cuda_stream)
+    assert torch.allclose(p, ref.detach(), atol=1e-6, rtol=1e-5)
+
+
+def test_bad_arguments_raise(ops):
+    with pytest.raises(RuntimeError):
+        ops.attention(*[torch.zeros(1, 1, 8, 12, dtype=torch.bfloat16, device=_dev())] * 3, 2)   # D=6
+    with pytest.raises(RuntimeError):
+        ops.layernorm_c(torch.zeros(1, 2, 2, 24, dtype=torch.bfloat16, device=_dev()),
+                        torch.ones(24, device=_dev()), torch.zeros(24, device=_dev()))
