@@ -141,7 +141,7 @@ def avgpool2(x):
 # ----------------------------------------------------------------------------
 # packed-weight cache (derived bf16 copies; the fp32 Parameter stays the truth)
 # ----------------------------------------------------------------------------
-_pack_cache = weakref.WeakKeyDictionary()
+_pack_cache = {}          # id(owner tensor) -> entry; dropped by a weakref callback
 
 
 def _packed(w, kind, Cpad):
@@ -151,11 +151,12 @@ def _packed(w, kind, Cpad):
              'tdgrad' convT IOHW as [Cin][(kh,kw,co)]         (k2 s2 conv of dy)"""
     owner = w._base if w._base is not None else w
     key = (kind, Cpad, w.storage_offset(), tuple(w.shape))
-    ent = _pack_cache.get(owner)
+    oid = id(owner)
+    ent = _pack_cache.get(oid)
     ver = (owner._version, owner.data_ptr())
-    if ent is None or ent.get("ver") != ver:
-        ent = {"ver": ver}
-        _pack_cache[owner] = ent
+    if ent is None or ent["ref"]() is not owner or ent.get("ver") != ver:
+        ent = {"ver": ver, "ref": weakref.ref(owner, lambda _r, oid=oid: _pack_cache.pop(oid, None))}
+        _pack_cache[oid] = ent
     if key in ent:
         return ent[key]
     src = w.detach()
