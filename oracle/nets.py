@@ -59,9 +59,46 @@ class Ctx:
         return F.dropout(x, p, True)
 
 
+# ---- optional emulation of the product path's bf16 rounding points ------------
+# With ``with nets.bf16_emulation():`` every conv/linear operand and every stored
+# activation is rounded to bf16 (straight-through in backward) exactly where the
+# CUDA path rounds, while all accumulation stays fp32.  Tests use it to separate
+# "kernel is wrong" from "bf16 storage loses precision" (parity).
+_EMU = [False]
+
+
+class bf16_emulation:
+    def __enter__(self):
+        self.prev = _EMU[0]
+        _EMU[0] = True
+
+    def __exit__(self, *a):
+        _EMU[0] = self.prev
+
+
+class _RoundSTE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, t):
+        return t.to(torch.bfloat16).to(t.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def _q(t):
+    return _RoundSTE.apply(t) if _EMU[0] else t
+
+
+def _conv2d(x, w, b=None, stride=1, padding=0, dilation=1, groups=1, wq=True):
+    """F.conv2d with bf16 operands under emulation (weights of the depthwise
+    projections stay fp32 in the product, wq=False)."""
+    return F.conv2d(_q(x), _q(w) if wq else w, b, stride, padding, dilation, groups)
+
+
 def _conv(sd: SD, name: str, x, stride=1, padding=1, dilation=1, groups=1):
-    return F.conv2d(x, sd[name + ".weight"], sd.get(name + ".bias"), stride,
-                    padding, dilation, groups)
+    return _conv2d(x, sd[name + ".weight"], sd.get(name + ".bias"), stride,
+                   padding, dilation, groups, wq=(groups == 1))
 
 
 def _ln_c(sd: SD, name: str, x):
@@ -69,11 +106,12 @@ def _ln_c(sd: SD, name: str, x):
     c = x.shape[1]
     y = F.layer_norm(x.permute(0, 2, 3, 1), (c,), sd[name + ".weight"],
                      sd[name + ".bias"], 1e-5)
-    return y.permute(0, 3, 1, 2)
+    return _q(y.permute(0, 3, 1, 2))
 
 
 def _bn(sd: SD, name: str, x, ctx: Ctx):
     """BatchNorm2d, batch statistics in training (UNet.py:59)."""
+    x = _q(x)
     rm, rv = sd[name + ".running_mean"], sd[name + ".running_var"]
     if ctx.training:
         rm, rv = rm.clone(), rv.clone()
@@ -100,13 +138,17 @@ def mha(sd: SD, p: str, q, k, v, heads: int):
     B, N, C = q.shape
     d = C // heads
     w, b = sd[p + ".in_proj_weight"], sd[p + ".in_proj_bias"]
-    qp = F.linear(q, w[:C], b[:C]).view(B, N, heads, d).transpose(1, 2)
-    kp = F.linear(k, w[C:2 * C], b[C:2 * C]).view(B, N, heads, d).transpose(1, 2)
-    vp = F.linear(v, w[2 * C:], b[2 * C:]).view(B, N, heads, d).transpose(1, 2)
+    qp = _q(F.linear(_q(q), _q(w[:C]), b[:C])).view(B, N, heads, d).transpose(1, 2)
+    kp = _q(F.linear(_q(k), _q(w[C:2 * C]), b[C:2 * C])).view(B, N, heads, d).transpose(1, 2)
+    vp = _q(F.linear(_q(v), _q(w[2 * C:]), b[2 * C:])).view(B, N, heads, d).transpose(1, 2)
     s = torch.matmul(qp, kp.transpose(-1, -2)) / math.sqrt(d)
-    o = torch.matmul(torch.softmax(s, dim=-1), vp)
-    o = o.transpose(1, 2).reshape(B, N, C)
-    return F.linear(o, sd[p + ".out_proj.weight"], sd[p + ".out_proj.bias"])
+    if _EMU[0]:   # flash form: un-normalised probabilities are rounded, the row sum is not
+        e = torch.exp(s - s.amax(dim=-1, keepdim=True))
+        o = torch.matmul(_q(e), vp) / e.sum(dim=-1, keepdim=True)
+    else:
+        o = torch.matmul(torch.softmax(s, dim=-1), vp)
+    o = _q(o.transpose(1, 2).reshape(B, N, C))
+    return _q(F.linear(o, _q(sd[p + ".out_proj.weight"]), sd[p + ".out_proj.bias"]))
 
 
 def fct_attention(sd: SD, p: str, x, heads=2):
@@ -114,7 +156,7 @@ def fct_attention(sd: SD, p: str, x, heads=2):
     B, C, H, W = x.shape
     proj = []
     for t in "qkv":
-        y = F.relu(_conv(sd, f"{p}.conv_{t}", x, groups=C))
+        y = F.relu(_conv(sd, f"{p}.conv_{t}", x, groups=C))      # fused with LN in the product: no rounding here
         y = _ln_c(sd, f"{p}.layernorm_{t}", y)
         proj.append(y.reshape(B, C, H * W).permute(0, 2, 1))
     o = mha(sd, p + ".attention", proj[0], proj[1], proj[2], heads)
@@ -125,42 +167,42 @@ def fct_wide_focus(sd: SD, p: str, x, ctx: Ctx):
     """Wide_Focus.forward, FCT.py:117-132."""
     acc = None
     for i, dil in ((1, 1), (2, 2), (3, 3)):
-        y = F.gelu(_conv(sd, f"{p}.conv{i}", x, padding=dil, dilation=dil))
+        y = _q(F.gelu(_q(_conv(sd, f"{p}.conv{i}", x, padding=dil, dilation=dil))))
         y = ctx.drop(y, 0.1, f"{p}.drop{i}")
         acc = y if acc is None else acc + y
-    y = F.gelu(_conv(sd, f"{p}.conv4", acc))
+    y = _q(F.gelu(_q(_conv(sd, f"{p}.conv4", _q(acc)))))
     return ctx.drop(y, 0.1, f"{p}.drop4")
 
 
 def fct_transformer(sd: SD, p: str, x, ctx: Ctx):
     """Transformer.forward, FCT.py:93-102."""
     a = fct_attention(sd, p + ".attention_output", x)
-    x2 = _conv(sd, p + ".conv1", a) + x
+    x2 = _q(_conv(sd, p + ".conv1", a) + x)
     x3 = fct_wide_focus(sd, p + ".wide_focus", _ln_c(sd, p + ".layernorm", x2), ctx)
-    return x2 + x3
+    return _q(x2 + x3)
 
 
 def fct_enc_block(sd: SD, p: str, blk: str, x, scale_img, ctx: Ctx, with_trans=True):
     """Block_encoder_bottleneck.forward (FCT.py:149-162) and, with
     with_trans=False, EncoderBlock.forward (AutoEncoder.py:17-27)."""
     if blk in ("first", "bottleneck"):
-        y = F.relu(_conv(sd, p + ".conv1_a", x))
-        y = F.relu(_conv(sd, p + ".conv2", y))
+        y = _q(F.relu(_conv(sd, p + ".conv1_a", x)))
+        y = _q(F.relu(_conv(sd, p + ".conv2", y)))
     else:
-        skip = F.relu(_conv(sd, p + ".conv1_b", scale_img))
+        skip = _q(F.relu(_conv(sd, p + ".conv1_b", scale_img)))
         y = torch.cat([skip, x], dim=1)
-        y = F.relu(_conv(sd, p + ".conv2", y))
-        y = F.relu(_conv(sd, p + ".conv3", y))
+        y = _q(F.relu(_conv(sd, p + ".conv2", y)))
+        y = _q(F.relu(_conv(sd, p + ".conv3", y)))
     y = F.max_pool2d(ctx.drop(y, 0.3, p + ".drop"), 2)
     return fct_transformer(sd, p + ".trans", y, ctx) if with_trans else y
 
 
 def fct_dec_block(sd: SD, p: str, x, skip, ctx: Ctx):
     """Block_decoder.forward, FCT.py:178-186."""
-    y = F.relu(_conv(sd, p + ".conv1", _up2(x)))
+    y = _q(F.relu(_conv(sd, p + ".conv1", _up2(x))))
     y = torch.cat((skip, y), dim=1)
-    y = F.relu(_conv(sd, p + ".conv2", y))
-    y = F.relu(_conv(sd, p + ".conv3", y))
+    y = _q(F.relu(_conv(sd, p + ".conv2", y)))
+    y = _q(F.relu(_conv(sd, p + ".conv3", y)))
     y = ctx.drop(y, 0.3, p + ".drop")
     return fct_transformer(sd, p + ".trans", y, ctx)
 
@@ -168,9 +210,10 @@ def fct_dec_block(sd: SD, p: str, x, skip, ctx: Ctx):
 def fct_forward(sd: SD, x, ctx: Optional[Ctx] = None, pre_sigmoid=False):
     """FCT.forward, FCT.py:235-254."""
     ctx = ctx or Ctx()
-    s2 = F.avg_pool2d(x, 2)
-    s3 = F.avg_pool2d(s2, 2)
-    s4 = F.avg_pool2d(s3, 2)
+    x = _q(x)
+    s2 = _q(F.avg_pool2d(x, 2))
+    s3 = _q(F.avg_pool2d(s2, 2))
+    s4 = _q(F.avg_pool2d(s3, 2))
     x1 = fct_enc_block(sd, "block_1", "first", x, None, ctx)
     x2 = fct_enc_block(sd, "block_2", "second", x1, s2, ctx)
     x3 = fct_enc_block(sd, "block_3", "third", x2, s3, ctx)
@@ -181,10 +224,10 @@ def fct_forward(sd: SD, x, ctx: Optional[Ctx] = None, pre_sigmoid=False):
     y = fct_dec_block(sd, "block_8", y, x2, ctx)
     y = fct_dec_block(sd, "block_9", y, x1, ctx)
     # DS_out.forward, FCT.py:201-206
-    y = F.relu(_conv(sd, "ds.conv1", _up2(y)))
-    y = F.relu(_conv(sd, "ds.conv2", y))
+    y = _q(F.relu(_conv(sd, "ds.conv1", _up2(y))))
+    y = _q(F.relu(_conv(sd, "ds.conv2", y)))
     z = _conv(sd, "ds.conv3", y)
-    return z if pre_sigmoid else torch.sigmoid(z)
+    return _q(z) if pre_sigmoid else _q(torch.sigmoid(z))
 
 
 # --------------------------------------------------------------------------
@@ -193,8 +236,8 @@ def fct_forward(sd: SD, x, ctx: Optional[Ctx] = None, pre_sigmoid=False):
 def _unet_block(sd: SD, p: str, name: str, x, ctx: Ctx):
     """UNet._block, UNet.py:54-66: [conv3x3(no bias) -> BN -> ReLU] x2."""
     for i in (1, 2):
-        x = F.conv2d(x, sd[f"{p}.{name}conv{i}.weight"], None, 1, 1)
-        x = F.relu(_bn(sd, f"{p}.{name}norm{i}", x, ctx))
+        x = _conv2d(x, sd[f"{p}.{name}conv{i}.weight"], None, 1, 1)
+        x = _q(F.relu(_bn(sd, f"{p}.{name}norm{i}", x, ctx)))
     return x
 
 
@@ -202,18 +245,19 @@ def unet_forward(sd: SD, x, ctx: Optional[Ctx] = None, pre_sigmoid=False, prefix
     """UNet.forward, UNet.py:32-51."""
     ctx = ctx or Ctx()
     P = prefix
+    x = _q(x)
     e1 = _unet_block(sd, P + "encoder1", "enc1", x, ctx)
     e2 = _unet_block(sd, P + "encoder2", "enc2", F.max_pool2d(e1, 2), ctx)
     e3 = _unet_block(sd, P + "encoder3", "enc3", F.max_pool2d(e2, 2), ctx)
     e4 = _unet_block(sd, P + "encoder4", "enc4", F.max_pool2d(e3, 2), ctx)
     y = _unet_block(sd, P + "bottleneck", "bottleneck", F.max_pool2d(e4, 2), ctx)
     for lvl, skip in ((4, e4), (3, e3), (2, e2), (1, e1)):
-        y = F.conv_transpose2d(y, sd[f"{P}upconv{lvl}.weight"],
-                               sd[f"{P}upconv{lvl}.bias"], stride=2)
+        y = _q(F.conv_transpose2d(_q(y), _q(sd[f"{P}upconv{lvl}.weight"]),
+                                  sd[f"{P}upconv{lvl}.bias"], stride=2))
         y = torch.cat((y, skip), dim=1)
         y = _unet_block(sd, f"{P}decoder{lvl}", f"dec{lvl}", y, ctx)
-    z = F.conv2d(y, sd[P + "conv.weight"], sd[P + "conv.bias"])
-    return z if pre_sigmoid else torch.sigmoid(z)
+    z = _conv2d(y, sd[P + "conv.weight"], sd[P + "conv.bias"])
+    return _q(z) if pre_sigmoid else _q(torch.sigmoid(z))
 
 
 # --------------------------------------------------------------------------
@@ -223,9 +267,10 @@ def autoencoder_forward(sd: SD, x, ctx: Optional[Ctx] = None, prefix=""):
     """AutoEncoder.forward (AutoEncoder.py:131-134) -> (latent, output)."""
     ctx = ctx or Ctx()
     E = prefix + "encoder."
-    s2 = F.avg_pool2d(x, 2)
-    s3 = F.avg_pool2d(s2, 2)
-    s4 = F.avg_pool2d(s3, 2)          # scale_img_5 (AutoEncoder.py:92) is dead
+    x = _q(x)
+    s2 = _q(F.avg_pool2d(x, 2))
+    s3 = _q(F.avg_pool2d(s2, 2))
+    s4 = _q(F.avg_pool2d(s3, 2))          # scale_img_5 (AutoEncoder.py:92) is dead
     x1 = fct_enc_block(sd, E + "block_1", "first", x, None, ctx, False)
     x2 = fct_enc_block(sd, E + "block_2", "second", x1, s2, ctx, False)
     x3 = fct_enc_block(sd, E + "block_3", "third", x2, s3, ctx, False)
@@ -235,14 +280,14 @@ def autoencoder_forward(sd: SD, x, ctx: Optional[Ctx] = None, prefix=""):
     D = prefix + "decoder."
     for b in (4, 3, 2, 1):            # DecoderBlock.forward, AutoEncoder.py:42-48
         p = f"{D}block_{b}"
-        y = F.relu(_conv(sd, p + ".conv1", _up2(y)))
-        y = F.relu(_conv(sd, p + ".conv2", y))
-        y = F.relu(_conv(sd, p + ".conv3", y))
+        y = _q(F.relu(_conv(sd, p + ".conv1", _up2(y))))
+        y = _q(F.relu(_conv(sd, p + ".conv2", y)))
+        y = _q(F.relu(_conv(sd, p + ".conv3", y)))
         y = ctx.drop(y, 0.3, p + ".drop")
     # DeepSupervisionBlock.forward, AutoEncoder.py:63-68 (ReLU head)
-    y = F.relu(_conv(sd, D + "ds.conv1", _up2(y)))
-    y = F.relu(_conv(sd, D + "ds.conv2", y))
-    y = F.relu(_conv(sd, D + "ds.conv3", y))
+    y = _q(F.relu(_conv(sd, D + "ds.conv1", _up2(y))))
+    y = _q(F.relu(_conv(sd, D + "ds.conv2", y)))
+    y = _q(F.relu(_conv(sd, D + "ds.conv3", y)))
     return latent, y
 
 
@@ -260,19 +305,19 @@ def i2i2m_forward(sd: SD, x, ctx: Optional[Ctx] = None):
 # --------------------------------------------------------------------------
 def _bottleneck(sd: SD, p: str, x, stride: int, ctx: Ctx):
     """Bottleneck.forward, pyc:AE_32K:L34-52."""
-    y = F.relu(_bn(sd, p + ".bn1", F.conv2d(x, sd[p + ".conv1.weight"]), ctx))
-    y = F.relu(_bn(sd, p + ".bn2",
-                   F.conv2d(y, sd[p + ".conv2.weight"], None, stride, 1), ctx))
-    y = _bn(sd, p + ".bn3", F.conv2d(y, sd[p + ".conv3.weight"]), ctx)
+    y = _q(F.relu(_bn(sd, p + ".bn1", _conv2d(x, sd[p + ".conv1.weight"]), ctx)))
+    y = _q(F.relu(_bn(sd, p + ".bn2",
+                   _conv2d(y, sd[p + ".conv2.weight"], None, stride, 1), ctx)))
+    y = _bn(sd, p + ".bn3", _conv2d(y, sd[p + ".conv3.weight"]), ctx)
     if p + ".downsample.0.weight" in sd:
-        x = _bn(sd, p + ".downsample.1",
-                F.conv2d(x, sd[p + ".downsample.0.weight"], None, stride), ctx)
-    return F.relu(y + x)
+        x = _q(_bn(sd, p + ".downsample.1",
+                   _conv2d(x, sd[p + ".downsample.0.weight"], None, stride), ctx))
+    return _q(F.relu(y + x))
 
 
 def encoder32k_forward(sd: SD, x, ctx: Ctx, p=""):
     """Encoder_32K.forward, pyc:AE_32K:L104-115 -> [B,8,H/4,W/4]."""
-    y = F.relu(_bn(sd, p + "bn1", F.conv2d(x, sd[p + "conv1.weight"], None, 2, 3), ctx))
+    y = _q(F.relu(_bn(sd, p + "bn1", _conv2d(x, sd[p + "conv1.weight"], None, 2, 3), ctx)))
     for i in range(3):
         y = _bottleneck(sd, f"{p}layer1.{i}", y, 1, ctx)
     y = ctx.drop(y, 0.3, p + "drop1", True)
@@ -280,27 +325,27 @@ def encoder32k_forward(sd: SD, x, ctx: Ctx, p=""):
         y = _bottleneck(sd, f"{p}layer2.{i}", y, 2 if i == 0 else 1, ctx)
     y = ctx.drop(y, 0.3, p + "drop2", True)
     for i in (2, 3, 4):
-        y = F.relu(_bn(sd, f"{p}bn{i}", _conv(sd, f"{p}conv{i}", y), ctx))
+        y = _q(F.relu(_bn(sd, f"{p}bn{i}", _conv(sd, f"{p}conv{i}", y), ctx)))
     y = ctx.drop(_conv(sd, p + "conv5", y), 0.3, p + "drop3", True)  # L113 order
-    return F.relu(_bn(sd, p + "bn5", y, ctx))
+    return _q(F.relu(_bn(sd, p + "bn5", y, ctx)))
 
 
 def decoder32k_forward(sd: SD, x, ctx: Ctx, p="", pre_activation=False):
     """Decoder_32K.forward, pyc:AE_32K:L162-168."""
     y = x
     for i in (1, 2, 3, 4):
-        y = F.relu(_bn(sd, f"{p}bn{i}", _conv(sd, f"{p}conv{i}", y), ctx))
-    y = F.conv_transpose2d(y, sd[p + "transConv1.weight"], sd[p + "transConv1.bias"], stride=2)
-    y = F.relu(_bn(sd, p + "dbn2", y, ctx))
-    y = F.conv_transpose2d(y, sd[p + "transConv2.weight"], sd[p + "transConv2.bias"], stride=2)
-    y = F.relu(_bn(sd, p + "dbn3", y, ctx))
-    y = F.relu(_bn(sd, p + "bn5", _conv(sd, p + "conv5", y), ctx))
-    y = F.relu(_bn(sd, p + "bn6", _conv(sd, p + "conv6", y), ctx))
+        y = _q(F.relu(_bn(sd, f"{p}bn{i}", _conv(sd, f"{p}conv{i}", y), ctx)))
+    y = _q(F.conv_transpose2d(_q(y), _q(sd[p + "transConv1.weight"]), sd[p + "transConv1.bias"], stride=2))
+    y = _q(F.relu(_bn(sd, p + "dbn2", y, ctx)))
+    y = _q(F.conv_transpose2d(_q(y), _q(sd[p + "transConv2.weight"]), sd[p + "transConv2.bias"], stride=2))
+    y = _q(F.relu(_bn(sd, p + "dbn3", y, ctx)))
+    y = _q(F.relu(_bn(sd, p + "bn5", _conv(sd, p + "conv5", y), ctx)))
+    y = _q(F.relu(_bn(sd, p + "bn6", _conv(sd, p + "conv6", y), ctx)))
     z = _bn(sd, p + "outputDeterminerNorm", _conv(sd, p + "outputDeterminerConv", y), ctx)
     if pre_activation:
         return z
     is_mask = sd[p + "outputDeterminerConv.weight"].shape[0] == 1
-    return torch.sigmoid(z) if is_mask else F.relu(z)
+    return _q(torch.sigmoid(z) if is_mask else F.relu(z))
 
 
 def ae32k_forward(sd: SD, x, ctx: Optional[Ctx] = None, enc="encoder.", dec="decoder."):
