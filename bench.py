@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""Headline benchmark: train frames/sec (fwd+bwd, 256x256) of the hybrid segmentation nets.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload ae32k_image|fct|unet|...]
+  python bench.py --impl reference ...      # the reference's CPU arithmetic on the host cores
+
+Own arm: one process per GPU (torchrun sets RANK/LOCAL_RANK/WORLD_SIZE); a step is
+zero_grad -> forward -> loss -> backward (-> NCCL gradient all-reduce when N>1) over one batch of
+synthetic frames; weights are re-packed every step as in real training.  One JSON line on rank 0.
+"""
+import argparse
+import contextlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+# workload -> (model key, per-GPU batch, loss, reference/BASELINE config string)
+WORKLOADS = {
+    "ae32k_image": ("ae32k_image", 16, "mse", "Autoencoder32K('image') 256->32K-latent image2image, fwd+bwd (BASELINE configs[1])"),
+    "fct": ("fct", 32, "dice", "FCT conv-attention net, batch 32, fwd+bwd (BASELINE configs[2])"),
+    "unet": ("unet", 32, "dice", "UNet fwd+bwd (BASELINE configs[0] shape on GPU)"),
+    "autoencoder": ("autoencoder", 64, "mse", "AutoEncoder (8K latent) fwd+bwd"),
+    "i2i2m": ("i2i2m", 16, "dice", "Image2Image2Mask (AE -> UNet) fwd+bwd (BASELINE configs[3] ii)"),
+    "latent2mask": ("latent2mask", 16, "dice", "latent-to-mask: frozen Encoder_32K -> Decoder_32K('mask') training (BASELINE configs[3] i)"),
+}
+DEFAULT_WORKLOAD = "ae32k_image"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm": d["hbm_gbs"], "tensor": d["bf16_tflops_sustained"], "tensor_burst": d["bf16_tflops"], "src": "measured"}
+    return {"hbm": 6650.0, "tensor": 1400.0, "tensor_burst": 1590.0, "src": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], False
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=3)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def make_batch(B, seed, device, pinned=False):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.rand(B, 3, 256, 256, generator=g)
+    y = (torch.rand(B, 1, 256, 256, generator=g) > 0.5).float()
+    if pinned:
+        return x.pin_memory(), y.pin_memory()
+    return x.to(device), y.to(device)
+
+
+def loss_fn(kind, out, x, y):
+    out = out[-1] if isinstance(out, tuple) else out
+    if kind == "mse":
+        return torch.nn.functional.mse_loss(out, x)
+    p, t = out[:, 0].reshape(-1), y[:, 0].reshape(-1)          # DiceLoss, Metrics.py:14-22
+    return 1.0 - (2.0 * torch.dot(p, t) + 1.0) / (p.sum() + t.sum() + 1.0)
+
+
+# ---------------------------------------------------------------------------------------------
+# per-kernel roofline pass: CUDA events around every C-ABI call of one extra step
+# ---------------------------------------------------------------------------------------------
+def _conv_work(args):
+    d = args[0]
+    n = 4 * d.pshuf if d.pshuf else d.Cout
+    flops = 2.0 * d.B * d.OH * d.OW * n * d.KH * d.KW * (d.C1 + d.C2)
+    if d.mode == 1 and d.stride > 1:
+        flops /= d.stride * d.stride
+    byt = 2.0 * d.B * (d.H * d.W * (d.C1 + d.C2) / (4 if d.ups else 1) + d.OH * d.OW * n)
+    return flops, byt
+
+
+def _attn_work(args, bwd):
+    if bwd:
+        B, N, heads, D = args[10], args[11], args[12], args[13]
+    else:
+        B, N, heads, D = args[5], args[6], args[7], args[8]
+    f = 4.0 * B * heads * N * N * D
+    return (2.5 * f if bwd else f), 2.0 * B * N * heads * D * (8 if bwd else 4)
+
+
+WORK = {
+    "hn_conv2d_fwd": lambda a: _conv_work(a),
+    "hn_conv3x3_tc_fwd": lambda a: _conv_work(a),
+    "hn_conv2d_wgrad": lambda a: _conv_work(a),
+    "hn_attn_fwd": lambda a: _attn_work(a, False),
+    "hn_attn_bwd": lambda a: _attn_work(a, True),
+}
+
+
+class KernelProfiler:
+    def __init__(self):
+        self.events = []        # (name, start, end, flops, bytes)
+
+    @contextlib.contextmanager
+    def __call__(self, name, args):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fl, by = WORK[name](args) if name in WORK else (0.0, 0.0)
+        s.record()
+        yield
+        e.record()
+        self.events.append((name, s, e, fl, by))
+
+    def table(self):
+        torch.cuda.synchronize()
+        agg = {}
+        for name, s, e, fl, by in self.events:
+            a = agg.setdefault(name, {"ms": 0.0, "n": 0, "flops": 0.0, "bytes": 0.0})
+            a["ms"] += s.elapsed_time(e)
+            a["n"] += 1
+            a["flops"] += fl
+            a["bytes"] += by
+        return agg
+
+
+def roofline_from(agg, steps, peaks):
+    total = sum(a["ms"] for a in agg.values())
+    name, a = max(agg.items(), key=lambda kv: kv[1]["ms"])
+    sec = a["ms"] / 1e3
+    tf = a["flops"] / sec / 1e12 if sec > 0 else 0.0
+    gbs = a["bytes"] / sec / 1e9 if sec > 0 else 0.0
+    tensor_frac, hbm_frac = tf / peaks["tensor"], gbs / peaks["hbm"]
+    if a["flops"] > 0 and tensor_frac >= hbm_frac:
+        r = {"bound": "tensor", "achieved": round(tf, 2), "peak": peaks["tensor"], "unit": "TFLOP/s", "frac": round(tensor_frac, 4)}
+    else:
+        r = {"bound": "hbm", "achieved": round(gbs, 1), "peak": peaks["hbm"], "unit": "GB/s", "frac": round(hbm_frac, 4)}
+    r.update({"kernel": name, "traffic": None, "peak_source": peaks["src"] + (" (sustained)" if r["bound"] == "tensor" else ""),
+              "launches_per_step": a["n"] // steps, "avg_launch_us": round(a["ms"] * 1e3 / a["n"], 1),
+              "share_of_step": round(a["ms"] / total, 3),
+              "algorithmic_per_launch": {"GFLOP": round(a["flops"] / a["n"] / 1e9, 3), "MB": round(a["bytes"] / a["n"] / 1e6, 2)}})
+    top = sorted(agg.items(), key=lambda kv: -kv[1]["ms"])[:6]
+    r["top_kernels"] = {k: {"share": round(v["ms"] / total, 3), "TFLOP/s": round(v["flops"] / (v["ms"] / 1e3) / 1e12, 1) if v["ms"] else 0,
+                            "GB/s": round(v["bytes"] / (v["ms"] / 1e3) / 1e9, 0) if v["ms"] else 0} for k, v in top}
+    return r
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle (CPU restatement of the reference's PyTorch path)
+# ---------------------------------------------------------------------------------------------
+def cpu_reference(workload, frames, steps, warmup):
+    """fwd+bwd of the reference arithmetic (oracle/nets.py, fp32, all host cores) on `frames` frames."""
+    from oracle import nets
+    key, _, kind, _ = WORKLOADS[workload]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = nets.init_state_dict(key, 0)
+    frozen = (lambda k: k.startswith("0.")) if key == "latent2mask" else (lambda k: False)
+    params = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running" not in k and not frozen(k) else v)
+              for k, v in sd.items()}
+    x, y = make_batch(frames, 1, "cpu")
+    ctx = nets.Ctx(training=True, dropout="on")
+    times = []
+    for i in range(warmup + steps):
+        for p in params.values():
+            if p.requires_grad:
+                p.grad = None
+        t0 = time.perf_counter()
+        out = nets.FORWARDS[key](params, x, ctx)
+        loss_fn(kind, out, x, y).backward()
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    sec = sum(times) / len(times)
+    return frames / sec, sec, cores
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU (default: the workload's)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dropout", action="store_true")
+    ap.add_argument("--kernel-table", action="store_true", help="print the per-kernel time table to stderr")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    key, B0, kind, cfg_name = WORKLOADS[args.workload]
+    B = args.batch or B0
+    metric, unit = "train frames/sec (fwd+bwd, 256x256)", "frames/s"
+    config = {"workload": cfg_name, "frames_per_gpu": B, "global_batch": B * world, "frame": "3x256x256 fp32 in [0,1)",
+              "parallelism": f"dp{world}" if world > 1 else "single", "l2": "activations per step >> 126 MB L2 (no flush needed)"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        frames = 2 if key in ("fct", "ae32k_image", "latent2mask", "i2i2m") else 4
+        steps = max(1, min(args.steps, 3))
+        fps, sec, cores = cpu_reference(args.workload, frames, steps, 1)
+        sample = f"{frames} frames x {steps} timed fwd+bwd passes of the same net (oracle port of the reference's PyTorch path, fp32)"
+        print(json.dumps({"impl": "reference", "metric": metric, "value": round(fps, 4), "unit": unit, "n_gpus": args.gpus,
+                          "steps": steps, "warmup": 1, "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": round(fps, 4), "unit": unit, "cores": cores, "kind": "port", "sample": sample},
+                          "e2e": {"value": round(fps, 4), "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch.distributed as dist
+    import hybridnet
+    from hybridnet import _lib, ops, parallel
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.call("hn_check_device")
+    torch.manual_seed(0)
+    model = hybridnet.MODELS[key]().to(dev).train()
+    if args.no_dropout:
+        for m in model.modules():
+            if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                m.p = 0.0
+    ops.manual_seed(1234 + rank)
+    dead = parallel.used_parameter_names(key)
+    used = {n for n, p in model.named_parameters() if p.requires_grad and n not in dead}
+    arena = parallel.GradArena(model, used=used, buckets=4)
+    x, y = make_batch(B, 1 + rank, dev)
+    xh, yh = make_batch(B, 1 + rank, dev, pinned=True)
+
+    def step(xd, yd):
+        arena.zero_grad()
+        ops.invalidate_packed()                 # weights change every step in training: pay for the repack
+        out = model(xd)
+        loss = loss_fn(kind, out, xd, yd)
+        loss.backward()
+        arena.finish()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(x, y)
+    barrier()
+    # ---- timed region 1: inputs resident in HBM ------------------------------------------------
+    _lib.stats["launches"] = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            loss = step(x, y)
+        e1.record()
+        barrier()
+    launches = _lib.stats["launches"]
+    ms = e0.elapsed_time(e1)
+    # ---- timed region 2: end to end through the public API with host buffers ---------------------
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    last = 0.0
+    for _ in range(args.steps):
+        xd = xh.to(dev, non_blocking=True)
+        yd = yh.to(dev, non_blocking=True)
+        last = float(step(xd, yd).item())          # device -> host read of the step's loss
+    e3.record()
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+
+    result = None
+    if rank == 0:
+        peaks = load_peaks()
+        # ---- roofline pass (not part of either timed region) -----------------------------------
+        prof = KernelProfiler()
+        _lib.set_profiler(prof)
+        psteps = 2
+        for _ in range(psteps):
+            step(x, y)
+        _lib.set_profiler(None)
+        agg = prof.table()
+        roof = roofline_from(agg, psteps, peaks)
+        if args.kernel_table:
+            tot = sum(a["ms"] for a in agg.values())
+            for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
+                print(f"{k:32s} {a['ms'] / psteps:9.3f} ms/step {100 * a['ms'] / tot:5.1f}%  n={a['n'] // psteps:4d}  "
+                      f"{a['flops'] / max(a['ms'], 1e-9) / 1e9:8.1f} TFLOP/s {a['bytes'] / max(a['ms'], 1e-9) / 1e6:8.0f} GB/s",
+                      file=sys.stderr)
+        from oracle.nets import GFLOP_PER_FRAME
+        gf = GFLOP_PER_FRAME[key][1]
+        fps = B * world * args.steps / (ms / 1e3)
+        fps_e2e = B * world * args.steps / (ms_e2e / 1e3)
+        result = {"metric": metric, "value": round(fps, 2), "unit": unit, "n_gpus": world, "steps": args.steps,
+                  "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
+                  "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+                  "clocks": clocks.summary(),
+                  "e2e": {"value": round(fps_e2e, 2), "unit": unit, "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4),
+                          "d2h_bytes_per_step": 4, "last_loss": round(last, 5)},
+                  "gpu_launches": launches,
+                  "model_tensor_roofline": {"GFLOP_per_frame_fwd_bwd": gf, "achieved_TFLOPs": round(fps / world * gf / 1e3, 2),
+                                            "frac_of_sustained_bf16": round(fps / world * gf / 1e3 / peaks["tensor"], 4)},
+                  "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            frames = 2
+            cfps, sec, cores = cpu_reference(args.workload, frames, 2, 1)
+            result["cpu_baseline"] = {"value": round(cfps, 4), "unit": unit, "cores": cores, "kind": "port",
+                                      "sample": f"{frames} frames x 2 timed fwd+bwd passes (oracle port of the reference's PyTorch path, fp32, {sec:.2f} s/pass)"}
+        print(json.dumps(result))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -90,9 +90,26 @@ def load():
     return lib
 
 
+# kernels launched per entry point (for the launch count bench.py reports)
+LAUNCHES = {"hn_attn_bwd": 3}
+stats = {"calls": 0, "launches": 0}
+_profiler = None      # optional callable(name, args) -> context manager (bench.py roofline pass)
+
+
+def set_profiler(p):
+    global _profiler
+    _profiler = p
+
+
 def call(name, *args):
     lib = load()
-    rc = getattr(lib, name)(*args)
+    stats["calls"] += 1
+    stats["launches"] += LAUNCHES.get(name, 1)
+    if _profiler is not None:
+        with _profiler(name, args):
+            rc = getattr(lib, name)(*args)
+    else:
+        rc = getattr(lib, name)(*args)
     if rc != 0:
         raise RuntimeError(f"{name} failed ({rc}): {lib.hn_last_error().decode()}")
 

@@ -186,6 +186,12 @@ def _packed(w, kind, Cpad):
     return ent[key]
 
 
+def invalidate_packed():
+    """Drop every derived bf16 weight copy (call after an optimizer step that bypasses ``_version``,
+    or to make a benchmark pay for the repack each step like real training does)."""
+    _pack_cache.clear()
+
+
 def _desc(**kw):
     d = HnConv()
     for k, v in kw.items():

@@ -1,0 +1,111 @@
+"""Data-parallel gradient exchange (the reference is single-process).
+
+One process per GPU.  All live gradients sit in ONE flat fp32 arena (``p.grad`` are views into
+it, never-used parameters -- SURVEY note U -- are excluded statically), split into a few
+buckets in reverse registration order (= the order backward produces them).  As soon as every
+gradient of a bucket has been accumulated, its slice is all-reduced (NCCL, sum) on a side
+stream, so the exchange overlaps the rest of backward; ``finish()`` joins the streams and
+scales by 1/world.  BatchNorm statistics stay per-rank (what DDP gives; the reference has no
+SyncBN).
+"""
+import torch
+import torch.distributed as dist
+
+
+class GradArena:
+    def __init__(self, model, used=None, buckets=4, process_group=None):
+        self.params = [p for n, p in model.named_parameters()
+                       if p.requires_grad and (used is None or n in used)]
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.group = process_group
+        n = sum(p.numel() for p in self.params)
+        dev = self.params[0].device
+        self.arena = torch.zeros(n, dtype=torch.float32, device=dev)
+        off = 0
+        self.slices = []
+        for p in self.params:
+            self.slices.append((off, off + p.numel()))
+            off += p.numel()
+        # buckets over the REVERSED parameter list (backward order), equal element counts
+        order = list(range(len(self.params)))[::-1]
+        per = max(1, n // max(1, buckets))
+        self.bucket_of = {}
+        self.bucket_range = []
+        cur, lo, hi, b = 0, None, None, 0
+        for i in order:
+            s, e = self.slices[i]
+            lo = s if lo is None else min(lo, s)
+            hi = e if hi is None else max(hi, e)
+            self.bucket_of[i] = b
+            cur += e - s
+            if cur >= per and b < buckets - 1:
+                self.bucket_range.append((lo, hi))
+                b, cur, lo, hi = b + 1, 0, None, None
+        if lo is not None:
+            self.bucket_range.append((lo, hi))
+        self.bucket_size = [0] * len(self.bucket_range)
+        for i in order:
+            self.bucket_size[self.bucket_of[i]] += 1
+        self.pending = list(self.bucket_size)
+        self.comm = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
+        self.works = []
+        self._attach()
+        if self.world > 1:
+            for i, p in enumerate(self.params):
+                p.register_post_accumulate_grad_hook(self._make_hook(i))
+
+    def _attach(self):
+        for p, (s, e) in zip(self.params, self.slices):
+            p.grad = self.arena[s:e].view_as(p)
+
+    def zero_grad(self):
+        """One memset instead of one per tensor; gradients stay views of the arena."""
+        self.arena.zero_()
+        self._attach()
+        self.pending = list(self.bucket_size)
+        self.works = []
+
+    def _make_hook(self, i):
+        def hook(_p):
+            b = self.bucket_of[i]
+            self.pending[b] -= 1
+            if self.pending[b] == 0:
+                self._launch(b)
+        return hook
+
+    def _launch(self, b):
+        lo, hi = self.bucket_range[b]
+        if self.comm is not None:
+            self.comm.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm):
+                self.works.append(dist.all_reduce(self.arena[lo:hi], op=dist.ReduceOp.SUM, group=self.group,
+                                                  async_op=True))
+        else:
+            dist.all_reduce(self.arena[lo:hi], op=dist.ReduceOp.SUM, group=self.group)
+
+    def finish(self):
+        """Join the exchange; gradients become the mean over ranks."""
+        if self.world == 1:
+            return
+        for b, left in enumerate(self.pending):       # buckets whose params got no grad this step
+            if left > 0:
+                self.pending[b] = 0
+                self._launch(b)
+        for w in self.works:
+            w.wait()
+        if self.comm is not None:
+            torch.cuda.current_stream().wait_stream(self.comm)
+        self.arena.mul_(1.0 / self.world)
+
+
+def used_parameter_names(model_name):
+    """Parameters that ever receive a gradient (SURVEY note U: 14 tensors of FCT / AutoEncoder never do)."""
+    dead = set()
+    if model_name in ("fct", "autoencoder", "i2i2m"):
+        pre = {"fct": "", "autoencoder": "encoder.", "i2i2m": "image2imageAE.encoder."}[model_name]
+        for blk, names in ((1, ("conv1_b", "conv3")), (2, ("conv1_a",)), (3, ("conv1_a",)), (4, ("conv1_a",)),
+                           (5, ("conv1_b", "conv3"))):
+            for nm in names:
+                dead.add(f"{pre}block_{blk}.{nm}.weight")
+                dead.add(f"{pre}block_{blk}.{nm}.bias")
+    return dead
