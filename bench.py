@@ -120,7 +120,7 @@ def _attn_work(args, bwd):
 
 WORK = {
     "hn_conv2d_fwd": lambda a: _conv_work(a),
-    "hn_conv3x3_tc_fwd": lambda a: _conv_work(a),
+    "hn_conv_tc_fwd": lambda a: _conv_work(a),
     "hn_conv2d_wgrad": lambda a: _conv_work(a),
     "hn_attn_fwd": lambda a: _attn_work(a, False),
     "hn_attn_bwd": lambda a: _attn_work(a, True),

@@ -174,9 +174,13 @@ int hn_attn_bwd(const void* q, const void* k, const void* v, const void* o, cons
                 int lddv, float scale, void* stream);
 
 /* ---- tcgen05/TMEM implicit-GEMM convolution (C >= 64 layers) ---------------- */
-/* 3x3 stride-1 conv, Cin%64==0, Cout%64==0, fed by TMA, accumulators in TMEM.   */
-int hn_conv3x3_tc_supported(const HnConv* d);
-int hn_conv3x3_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
+/* Same contract as hn_conv2d_fwd (no residual) for the geometries the tensor-core path takes:
+ * stride 1, "same" output extent, C1%64==0, C2%64==0, GEMM N a multiple of 32 (>= 64), pixel
+ * tiles of 128 (W a power of two <= 128 or a multiple of 128); 1x1 / 3x3 / dilated, ConvT k2s2
+ * through pshuf.  A: 4-D TMA boxes shifted per tap (OOB zero fill = padding), B: packed weights,
+ * accumulators in TMEM, persistent CTAs.  hn_conv_tc_supported() tells the host which path to use. */
+int hn_conv_tc_supported(const HnConv* d);
+int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
                       const float* bias, void* y, float* stat_sum, float* stat_sqsum,
                       void* stream);
 

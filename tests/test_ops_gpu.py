@@ -339,3 +339,99 @@ def test_bad_arguments_raise(ops):
     with pytest.raises(RuntimeError):
         ops.layernorm_c(torch.zeros(1, 2, 2, 24, dtype=torch.bfloat16, device=_dev()),
                         torch.ones(24, device=_dev()), torch.zeros(24, device=_dev()))
+
+
+TC_CASES = [
+    # Cin, Cin2, Cout, k, dil, B, H, W, stats
+    (64, 0, 64, 3, 1, 2, 16, 16, False),
+    (128, 0, 256, 3, 1, 1, 32, 32, True),
+    (64, 64, 128, 3, 1, 2, 8, 8, False),        # virtual concat, 8x8 maps: one 128-pixel tile = 2 images
+    (256, 0, 64, 1, 1, 1, 16, 128, False),      # 1x1, W = 128
+    (64, 0, 192, 3, 2, 1, 64, 64, True),        # dilation 2, N tile 192
+    (192, 0, 64, 3, 1, 1, 8, 256, False),       # W = 256 (two tiles per row)
+]
+
+
+@pytest.mark.parametrize("case", TC_CASES)
+def test_conv_tcgen05_path(ops, case):
+    """The tcgen05/TMEM/TMA kernel against PyTorch fp32 AND bit-for-bit-close to the mma.sync kernel."""
+    from hybridnet import _lib
+    Cin, Cin2, Cout, k, dil, B, H, W, stats = case
+    pad = dil * (k - 1) // 2
+    x = _rand(B, Cin, H, W, seed=2).requires_grad_(True)
+    x2 = _rand(B, Cin2, H, W, seed=12).requires_grad_(True) if Cin2 else None
+    w = _rand(Cout, Cin + Cin2, k, k, seed=3, scale=1.0 / math.sqrt((Cin + Cin2) * k * k)).requires_grad_(True)
+    b = _rand(Cout, seed=4, scale=0.1).requires_grad_(True)
+    xin = torch.cat([x, x2], 1) if Cin2 else x
+    ref = F.relu(F.conv2d(xin, w, b, 1, pad, dil))
+    gy = _rand(*ref.shape, seed=5)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (x, w, b)] + ([x2.grad.clone()] if Cin2 else [])
+    for t in (x, w, b, x2):
+        if t is not None:
+            t.grad = None
+    d = ops._desc(B=B, H=H, W=W, C1=Cin, C2=Cin2, ld1=Cin, ld2=Cin2, OH=H, OW=W, Cout=Cout, ldy=Cout, KH=k, KW=k,
+                  stride=1, pad=pad, dil=dil, mode=0, ups=0, act=1, pshuf=0, ldr=0, Kpad=k * k * (Cin + Cin2))
+    assert _lib.load().hn_conv_tc_supported(d) == 1
+    assert ops.USE_TC
+    calls = []
+    _lib.set_profiler(lambda name, args: (calls.append(name), __import__("contextlib").nullcontext())[1])
+    try:
+        y = ops.conv2d(ops.to_nhwc(x), w, b, x2=ops.to_nhwc(x2) if Cin2 else None, pad=pad, dil=dil, act="relu")
+        out = ops.to_nchw(y, Cout)
+        out.backward(gy)
+    finally:
+        _lib.set_profiler(None)
+    assert calls.count("hn_conv_tc_fwd") == 2, calls            # forward and (flipped-tap) input gradient
+    assert rel_l2(out, ref) < FWD_TOL
+    got = [x.grad, w.grad, b.grad] + ([x2.grad] if Cin2 else [])
+    for g, r in zip(got, want):
+        assert rel_l2(g, r) < BWD_TOL
+    # same op through the mma.sync kernel: identical up to fp32 summation order
+    ops.USE_TC = False
+    try:
+        y2 = ops.conv2d(ops.to_nhwc(x.detach()), w.detach(), b.detach(), x2=ops.to_nhwc(x2.detach()) if Cin2 else None,
+                        pad=pad, dil=dil, act="relu")
+    finally:
+        ops.USE_TC = True
+    assert rel_l2(y.float(), y2.float()) < 2e-3
+    if stats:
+        s = [torch.zeros(Cout, device=_dev()) for _ in range(4)]
+        wp, Kpad = ops._packed(w.detach(), "fwd", Cin + Cin2)
+        z1 = ops._conv_raw(ops.to_nhwc(x.detach()), None, wp, Kpad, b.detach(), None, OH=H, OW=W, Cout=Cout, KH=k, KW=k,
+                           stride=1, pad=pad, dil=dil, stats=(s[0], s[1]))
+        ops.USE_TC = False
+        try:
+            z2 = ops._conv_raw(ops.to_nhwc(x.detach()), None, wp, Kpad, b.detach(), None, OH=H, OW=W, Cout=Cout, KH=k,
+                               KW=k, stride=1, pad=pad, dil=dil, stats=(s[2], s[3]))
+        finally:
+            ops.USE_TC = True
+        zf = z1.float()
+        assert torch.allclose(s[0], zf.sum(dim=(0, 1, 2)), rtol=1e-3, atol=1e-2)
+        assert torch.allclose(s[1], (zf * zf).sum(dim=(0, 1, 2)), rtol=1e-3, atol=1e-2)
+        assert torch.allclose(s[0], s[2], rtol=2e-3, atol=5e-2) and torch.allclose(s[1], s[3], rtol=2e-3, atol=5e-2)
+
+
+def test_conv_transpose_tcgen05(ops):
+    from hybridnet import _lib
+    B, H, cin, cout = 2, 16, 256, 384
+    x = _rand(B, cin, H, H, seed=1).requires_grad_(True)
+    w = _rand(cin, cout, 2, 2, seed=2, scale=1.0 / math.sqrt(cin)).requires_grad_(True)
+    b = _rand(cout, seed=3, scale=0.1).requires_grad_(True)
+    ref = F.conv_transpose2d(x, w, b, stride=2)
+    gy = _rand(*ref.shape, seed=4)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (x, w, b)]
+    for t in (x, w, b):
+        t.grad = None
+    calls = []
+    _lib.set_profiler(lambda name, args: (calls.append(name), __import__("contextlib").nullcontext())[1])
+    try:
+        out = ops.to_nchw(ops.conv2d(ops.to_nhwc(x), w, b, stride=2, pad=0, transposed=True), cout)
+        out.backward(gy)
+    finally:
+        _lib.set_profiler(None)
+    assert "hn_conv_tc_fwd" in calls
+    assert rel_l2(out, ref) < FWD_TOL
+    for t, r in zip((x, w, b), want):
+        assert rel_l2(t.grad, r) < BWD_TOL

@@ -61,8 +61,8 @@ SIGNATURES = {
     "hn_attn_fwd": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _P, _P, _P, _I, _I, _I, _I,
                     _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
-    "hn_conv3x3_tc_supported": [POINTER(HnConv)],
-    "hn_conv3x3_tc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
+    "hn_conv_tc_supported": [POINTER(HnConv)],
+    "hn_conv_tc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
     "hn_adamw_step": [_FP, _FP, _FP, _FP, _L, _F, _F, _F, _F, _F, _I, _F, _P],
 }
 

@@ -8,6 +8,7 @@ heads are actually padded).  A channel slice ``t[..., a:b]`` of such a tensor is
 itself a valid operand (pixel stride = ld), which is how concat costs nothing.
 """
 import math
+import os
 import weakref
 
 import torch
@@ -141,6 +142,7 @@ def avgpool2(x):
 # ----------------------------------------------------------------------------
 # packed-weight cache (derived bf16 copies; the fp32 Parameter stays the truth)
 # ----------------------------------------------------------------------------
+USE_TC = os.environ.get("HN_DISABLE_TC", "0") != "1"     # tcgen05 path for the geometries it supports
 _pack_cache = {}          # id(owner tensor) -> entry; dropped by a weakref callback
 
 
@@ -162,6 +164,7 @@ def _packed(w, kind, Cpad):
     src = w.detach()
     assert src.dtype == torch.float32 and src.is_contiguous()
     d0, d1, KH, KW = src.shape
+    assert kind != "dgradf" or src.is_contiguous()
     big = 1 << 40
     if kind == "fwd":
         N, Creal, kh, kw = d0, d1, KH, KW
@@ -169,6 +172,10 @@ def _packed(w, kind, Cpad):
     elif kind == "dgrad":
         N, Creal, kh, kw = d1, d0, KH, KW
         args = (big, 0, KH * KW, d1 * KH * KW, KW, 1)
+    elif kind == "dgradf":      # stride-1 input gradient as a forward conv: taps flipped
+        N, Creal, kh, kw = d1, d0, KH, KW
+        args = (big, 0, KH * KW, d1 * KH * KW, -KW, -1)
+        src = src.reshape(-1)[KH * KW - 1:]
     elif kind == "tfwd":        # weight [Cin, Cout, 2, 2]; n = tap*Cout + co ; c = ci
         N, Creal, kh, kw = 4 * d1, d0, 1, 1
         args = (d1, 1, 4, d1 * 4, 0, 0)
@@ -225,6 +232,10 @@ def _conv_raw(x1, x2, wp, Kpad, bias, res, *, OH, OW, Cout, KH, KW, stride, pad,
     s0 = s1 = None
     if stats is not None:
         s0, s1 = stats
+    if res is None and USE_TC and _lib.load().hn_conv_tc_supported(d):
+        call("hn_conv_tc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
+             _ptr(s1), _stream())
+        return out
     call("hn_conv2d_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), _ptr(res), out.data_ptr(),
          _ptr(s0), _ptr(s1), _stream())
     return out
@@ -322,9 +333,14 @@ def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
             dx1 = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
                             dil=1)
         else:
-            wp, Kpad = _packed(weight, "dgrad", dz.shape[3])
-            full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=g.KH, KW=g.KW,
-                             stride=g.stride, pad=g.pad, dil=g.dil, mode=1, H=g.OH, W=g.OW)
+            if g.stride == 1:      # forward-gather form with flipped taps (tensor-core path eligible)
+                wp, Kpad = _packed(weight, "dgradf", dz.shape[3])
+                full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=g.KH, KW=g.KW,
+                                 stride=1, pad=g.dil * (g.KH - 1) - g.pad, dil=g.dil, mode=0, H=g.OH, W=g.OW)
+            else:
+                wp, Kpad = _packed(weight, "dgrad", dz.shape[3])
+                full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=g.KH, KW=g.KW,
+                                 stride=g.stride, pad=g.pad, dil=g.dil, mode=1, H=g.OH, W=g.OW)
             if full.shape[3] != C1 + C2:        # image input: Cin=3 padded to 8
                 assert C2 == 0 and full.shape[3] == C1
             if g.ups:
