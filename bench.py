@@ -122,6 +122,7 @@ WORK = {
     "hn_conv2d_fwd": lambda a: _conv_work(a),
     "hn_conv_tc_fwd": lambda a: _conv_work(a),
     "hn_conv2d_wgrad": lambda a: _conv_work(a),
+    "hn_conv_wgrad_tc": lambda a: _conv_work(a),
     "hn_attn_fwd": lambda a: _attn_work(a, False),
     "hn_attn_bwd": lambda a: _attn_work(a, True),
 }

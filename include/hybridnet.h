@@ -184,6 +184,14 @@ int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* 
                       const float* bias, void* y, float* stat_sum, float* stat_sqsum,
                       void* stream);
 
+/* tcgen05 weight gradient: same contract as hn_conv2d_wgrad for stride 1/2 convs with C1%64==0,
+ * C2%64==0, Cout>=64 and 64-pixel tileable output maps.  Per tap: D[Cout,Cin] = dz^T x_tap with both
+ * operands MN-major straight from TMA boxes, accumulators in TMEM, split over pixels + fp32 atomics. */
+int hn_conv_wgrad_tc_supported(const HnConv* d);
+int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2, const void* dy, float* dw,
+                     int Creal, long long s_n, long long s_c, long long s_kh, long long s_kw,
+                     void* stream);
+
 /* ---- fused multi-tensor AdamW on a flat fp32 arena (FCT.py:305,338) --------- */
 int hn_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
                   long long n, float lr, float beta1, float beta2, float eps, float weight_decay,

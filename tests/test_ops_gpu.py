@@ -383,6 +383,7 @@ def test_conv_tcgen05_path(ops, case):
     finally:
         _lib.set_profiler(None)
     assert calls.count("hn_conv_tc_fwd") == 2, calls            # forward and (flipped-tap) input gradient
+    assert calls.count("hn_conv_wgrad_tc") == 1, calls
     assert rel_l2(out, ref) < FWD_TOL
     got = [x.grad, w.grad, b.grad] + ([x2.grad] if Cin2 else [])
     for g, r in zip(got, want):
