@@ -129,13 +129,18 @@ WORK = {
 
 
 class KernelProfiler:
-    def __init__(self):
+    def __init__(self, detail=False):
+        self.detail = detail
         self.events = []        # (name, start, end, flops, bytes)
 
     @contextlib.contextmanager
     def __call__(self, name, args):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         fl, by = WORK[name](args) if name in WORK else (0.0, 0.0)
+        if self.detail and name.startswith("hn_conv"):
+            d = args[0]
+            name = (f"{name}[{d.B}x{d.H}x{d.W} C{d.C1}+{d.C2}->{4 * d.pshuf if d.pshuf else d.Cout} k{d.KH} s{d.stride} "
+                    f"d{d.dil} m{d.mode}{' st' if (len(args) > 8 and args[-3]) else ''}]")
         s.record()
         yield
         e.record()
@@ -214,6 +219,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dropout", action="store_true")
     ap.add_argument("--kernel-table", action="store_true", help="print the per-kernel time table to stderr")
+    ap.add_argument("--kernel-detail", action="store_true", help="per conv geometry rows in the kernel table")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
 
@@ -311,7 +317,7 @@ def main():
     if rank == 0:
         peaks = load_peaks()
         # ---- roofline pass (not part of either timed region) -----------------------------------
-        prof = KernelProfiler()
+        prof = KernelProfiler(args.kernel_detail)
         _lib.set_profiler(prof)
         psteps = 2
         for _ in range(psteps):
@@ -322,7 +328,7 @@ def main():
         if args.kernel_table:
             tot = sum(a["ms"] for a in agg.values())
             for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
-                print(f"{k:32s} {a['ms'] / psteps:9.3f} ms/step {100 * a['ms'] / tot:5.1f}%  n={a['n'] // psteps:4d}  "
+                print(f"{k:34s} {a['ms'] / psteps:9.3f} ms/step {100 * a['ms'] / tot:5.1f}%  n={a['n'] // psteps:4d}  "
                       f"{a['flops'] / max(a['ms'], 1e-9) / 1e9:8.1f} TFLOP/s {a['bytes'] / max(a['ms'], 1e-9) / 1e6:8.0f} GB/s",
                       file=sys.stderr)
         from oracle.nets import GFLOP_PER_FRAME
