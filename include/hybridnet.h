@@ -147,6 +147,17 @@ int hn_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* mean, 
                     const float* gamma, const float* s1, const float* s2, long long P, int C,
                     int lddz, int ldx, int lddx, int training, void* stream);
 
+/* BatchNorm + ReLU without residual (every UNet.py:58-63 block, most of pyc:AE_32K): the ReLU mask is
+ * re-derived from x with the exact fp32 expression hn_bn_apply used, so backward reads dy and x only
+ * (reduce: 2 passes, apply: 3) instead of dy,y,x(+dz). */
+int hn_bn_relu_bwd_reduce(const void* dy, const void* x, const float* mean, const float* rstd,
+                          const float* gamma, const float* beta, long long P, int C, int lddy,
+                          int ldx, float* s1, float* s2, void* stream);
+int hn_bn_relu_bwd_apply(const void* dy, const void* x, void* dx, const float* mean,
+                         const float* rstd, const float* gamma, const float* beta, const float* s1,
+                         const float* s2, long long P, int C, int lddy, int ldx, int lddx,
+                         int training, void* stream);
+
 /* ---- conv-projected attention (FCT.py:24-79) -------------------------------- */
 /* q,k,v = LayerNorm_C(ReLU(dwconv3x3(x)+b)) for the three projections in one pass.
  * w: [3][C][9] fp32, b: [3][C], gamma/beta: [3][C]; out: [3] tensors of [P,C]   */

@@ -54,6 +54,8 @@ SIGNATURES = {
     "hn_bn_apply": [_P, _P, _P, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _I, _I, _P],
     "hn_bn_bwd_reduce": [_P, _P, _P, _P, _FP, _FP, _L, _I, _I, _I, _I, _I, _I, _FP, _FP, _P],
     "hn_bn_bwd_apply": [_P, _P, _P, _FP, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _I, _I, _P],
+    "hn_bn_relu_bwd_reduce": [_P, _P, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _FP, _FP, _P],
+    "hn_bn_relu_bwd_apply": [_P, _P, _P, _FP, _FP, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _I, _I, _P],
     "hn_dwconv_relu_ln_fwd": [_P, _P, _P, _P, _FP, _FP, _FP, _FP, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_dwconv_relu_ln_bwd_pre": [_P, _P, _P, _P, _P, _P, _P, _FP, _FP, _FP, _FP, _FP, _FP,
                                   _I, _I, _I, _I, _I, _I, _F, _P],

@@ -98,18 +98,22 @@ __device__ __forceinline__ float apply_act(float v, int act) {
   return v;
 }
 
-// 8 x bf16 <-> 8 x float through one 16-byte access
-struct __align__(16) bf16x8 { bf162 v[4]; };
+// 8 x bf16 <-> 8 x float through ONE 16-byte access (uint4: a struct of four bf162 is copied
+// member-wise by nvcc and degrades to four 32-bit accesses)
 __device__ __forceinline__ void load8(const bf16* p, float* f) {
-  bf16x8 r = *reinterpret_cast<const bf16x8*>(p);
+  const uint4 r = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
-  for (int i = 0; i < 4; ++i) { float2 t = __bfloat1622float2(r.v[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
 }
 __device__ __forceinline__ void store8(bf16* p, const float* f) {
-  bf16x8 r;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) r.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-  *reinterpret_cast<bf16x8*>(p) = r;
+  uint4 r;
+  r.x = pack_bf16(f[0], f[1]); r.y = pack_bf16(f[2], f[3]);
+  r.z = pack_bf16(f[4], f[5]); r.w = pack_bf16(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = r;
 }
 
 // stateless counter-based RNG for dropout: one 32-bit hash per element index
@@ -119,4 +123,41 @@ __device__ __forceinline__ uint32_t hn_hash(uint64_t seed, uint64_t idx) {
   z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
   z = z ^ (z >> 31);
   return (uint32_t)(z >> 32);
+}
+__device__ __forceinline__ uint64_t hn_hash64(uint64_t seed, uint64_t idx) {
+  uint64_t z = idx * 0x9E3779B97F4A7C15ull + seed;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+// ---- column (per-channel) pass helpers ---------------------------------------------------
+// A thread owns channel vector cv = thread % CV (the launch makes the total thread count a
+// multiple of CV) and walks pixels pix0, pix0+pstride, ... -- no division in the loop.
+struct ColIter { long long pix0, pstride; int cv; };
+__device__ __forceinline__ ColIter col_iter(int CV) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long n = gridDim.x * (long long)blockDim.x;
+  ColIter it;
+  it.pix0 = t / CV; it.pstride = n / CV; it.cv = (int)(t - it.pix0 * CV);
+  return it;
+}
+// Fold 8 per-thread partial sums into s_acc[cv*8 .. +8).  When CV divides 32 the lanes of a
+// warp that share cv (lane % CV) are combined by shuffles first, so only CV lanes touch smem.
+// Must be called by all threads of the warp.
+__device__ __forceinline__ void col_fold8(float* s_acc, float* part, int cv, int CV) {
+  const int lane = threadIdx.x & 31;
+  if (CV < 32 && (CV & (CV - 1)) == 0) {
+    for (int o = CV; o < 32; o <<= 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) part[j] += __shfl_xor_sync(0xffffffffu, part[j], o);
+    }
+    if (lane < CV) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&s_acc[cv * 8 + j], part[j]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&s_acc[cv * 8 + j], part[j]);
+  }
 }

@@ -243,8 +243,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           pix = ((long long)b * (2 * p.H) + 2 * h + (tap >> 1)) * (2 * p.W) + 2 * w + (tap & 1);
         }
         float v[32];
+        if (p.bias == nullptr) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(p.bias + ch0 + j) : 0.f);
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        } else if ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + ch0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 bv = __ldg(b4 + j);
+            v[4 * j] = __uint_as_float(r[4 * j]) + bv.x; v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + bv.y;
+            v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + bv.z; v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + bv.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __ldg(p.bias + ch0 + j);
+        }
         if (p.ssum) {
           float t[32];
 #pragma unroll

@@ -152,8 +152,9 @@ __global__ void upsample2_bwd_kernel(const bf16* __restrict__ dy, bf16* __restri
 }
 
 // ---- activation backward (+ bias gradient) -----------------------------------------------
-__global__ void act_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ yz, bf16* __restrict__ dz,
-                               long long P, int C, int lddy, int ldy, int lddz, int act, float* __restrict__ dbias) {
+__global__ void __launch_bounds__(256) act_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ yz,
+                                                      bf16* __restrict__ dz, long long P, int C, int lddy, int ldy,
+                                                      int lddz, int act, float* __restrict__ dbias) {
   extern __shared__ float s_acc[];
   const int CV = C / 8;
   if (dbias) {
@@ -161,27 +162,34 @@ __global__ void act_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restri
     __syncthreads();
   }
   float part[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  long long total = P * CV;
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int cv = (int)(i0 % CV);
-  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
-    long long pix = i / CV;
-    float g[8], a[8], o[8];
-    load8(dy + pix * lddy + cv * 8, g);
-    if (act != HN_ACT_NONE) load8(yz + pix * ldy + cv * 8, a);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float v = g[j];
-      if (act == HN_ACT_RELU) v = a[j] > 0.f ? v : 0.f;
-      else if (act == HN_ACT_SIGMOID) v = v * a[j] * (1.f - a[j]);
-      else if (act == HN_ACT_GELU) v = v * gelu_grad_f(a[j]);
-      o[j] = v;
-      part[j] += bf16_round(v);
+  const ColIter it = col_iter(CV);
+  for (long long pix = it.pix0; pix < P; pix += 2 * it.pstride) {
+    const long long pix2 = pix + it.pstride;
+    const bool two = pix2 < P;
+    float g[2][8], a[2][8];
+    load8(dy + pix * lddy + it.cv * 8, g[0]);
+    if (two) load8(dy + pix2 * lddy + it.cv * 8, g[1]);
+    if (act != HN_ACT_NONE) {
+      load8(yz + pix * ldy + it.cv * 8, a[0]);
+      if (two) load8(yz + pix2 * ldy + it.cv * 8, a[1]);
     }
-    store8(dz + pix * lddz + cv * 8, o);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = g[u][j];
+        if (act == HN_ACT_RELU) v = a[u][j] > 0.f ? v : 0.f;
+        else if (act == HN_ACT_SIGMOID) v = v * a[u][j] * (1.f - a[u][j]);
+        else if (act == HN_ACT_GELU) v = v * gelu_grad_f(a[u][j]);
+        g[u][j] = v;
+        part[j] += bf16_round(v);
+      }
+      store8(dz + (u ? pix2 : pix) * lddz + it.cv * 8, g[u]);
+    }
   }
   if (dbias) {
-    col_flush(s_acc, part, cv, C, 1);
+    col_fold8(s_acc, part, it.cv, CV);
     __syncthreads();
     for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(dbias + i, s_acc[i]);
   }
@@ -198,22 +206,29 @@ __global__ void act_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
     store8(y + pix * ldy + cv * 8, f);
   }
 }
-__global__ void colsum_kernel(const bf16* __restrict__ x, long long P, int C, int ld, float* __restrict__ out) {
+__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long long P, int C, int ld,
+                                                     float* __restrict__ out) {
   extern __shared__ float s_acc[];
   const int CV = C / 8;
   for (int i = threadIdx.x; i < C; i += blockDim.x) s_acc[i] = 0.f;
   __syncthreads();
   float part[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  long long total = P * CV;
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int cv = (int)(i0 % CV);
-  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
-    float g[8];
-    load8(x + (i / CV) * ld + cv * 8, g);
+  const ColIter it = col_iter(CV);
+  for (long long pix = it.pix0; pix < P; pix += 4 * it.pstride) {
+    float g[4][8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) part[j] += g[j];
+    for (int u = 0; u < 4; ++u) {
+      const long long q = pix + u * it.pstride;
+      if (q < P) load8(x + q * ld + it.cv * 8, g[u]);
+      else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[u][j] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) part[j] += (g[0][j] + g[1][j]) + (g[2][j] + g[3][j]);
   }
-  col_flush(s_acc, part, cv, C, 1);
+  col_fold8(s_acc, part, it.cv, CV);
   __syncthreads();
   for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(out + i, s_acc[i]);
 }
@@ -265,24 +280,35 @@ __global__ void gelu3_bwd_kernel(const bf16* __restrict__ dy, const bf16* __rest
     store8(d1 + i * 8, a); store8(d2 + i * 8, b); store8(d3 + i * 8, c);
   }
 }
-__global__ void dropout_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int B, long long HW, int C, int ldx,
-                               int ldy, float p, unsigned long long seed, int channelwise) {
+// keep bit of element e = 16 random bits >= p*65536, four elements per 64-bit hash of (seed, e/4);
+// channelwise (Dropout2d): one hash per (b, c) plane index.
+__global__ void __launch_bounds__(256) dropout_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int B,
+                                                      long long HW, int C, int ldx, int ldy, float p,
+                                                      unsigned long long seed, int channelwise) {
   const int CV = C / 8;
-  long long total = (long long)B * HW * CV;
+  const long long P = (long long)B * HW;
   const float scale = 1.f / (1.f - p);
-  const uint32_t thr = (uint32_t)(p * 4294967296.0);
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    long long pix = i / CV;
-    int cv = (int)(i - pix * CV);
+  const uint32_t thr = (uint32_t)(p * 65536.0f);
+  const ColIter it = col_iter(CV);
+  for (long long pix = it.pix0; pix < P; pix += it.pstride) {
     float f[8];
-    load8(x + pix * ldx + cv * 8, f);
-    long long b = pix / HW;
+    load8(x + pix * ldx + it.cv * 8, f);
+    uint64_t r0, r1;
+    if (channelwise) {
+      const uint64_t base = (uint64_t)((pix / HW) * C + it.cv * 8);
+      r0 = hn_hash64(seed, base >> 2);
+      r1 = hn_hash64(seed, (base >> 2) + 1);
+    } else {
+      const uint64_t base = (uint64_t)(pix * C + it.cv * 8);
+      r0 = hn_hash64(seed, base >> 2);
+      r1 = hn_hash64(seed, (base >> 2) + 1);
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      uint64_t idx = channelwise ? (uint64_t)(b * C + cv * 8 + j) : (uint64_t)(pix * C + cv * 8 + j);
-      f[j] = hn_hash(seed, idx) >= thr ? f[j] * scale : 0.f;
+      const uint32_t bits = (uint32_t)((j < 4 ? r0 : r1) >> (16 * (j & 3))) & 0xFFFFu;
+      f[j] = bits >= thr ? f[j] * scale : 0.f;
     }
-    store8(y + pix * ldy + cv * 8, f);
+    store8(y + pix * ldy + it.cv * 8, f);
   }
 }
 }  // namespace
@@ -365,7 +391,7 @@ extern "C" int hn_gelu3_sum_bwd(const void* dy, const void* z1, const void* z2, 
   return HN_OK;
 }
 extern "C" int hn_dropout(const void* x, void* y, int B, long long HW, int C, int ldx, int ldy, float p, unsigned long long seed, int channelwise, void* stream) {
-  REQ_C8(C, "dropout");
+  REQ_CV(C, "dropout");
   HN_REQUIRE(x && y && p >= 0.f && p < 1.f, "dropout: bad args");
   dropout_kernel<<<grid_for((long long)B * HW * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (bf16*)y, B, HW, C, ldx, ldy, p, seed, channelwise);
   HN_CHECK_LAUNCH("dropout");

@@ -102,27 +102,29 @@ __global__ void ln_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict
 }
 
 // ---- BatchNorm ----------------------------------------------------------------------
-__global__ void bn_stats_kernel(const bf16* __restrict__ x, long long P, int C, int ld, float* __restrict__ sum,
-                                float* __restrict__ sq) {
+// All passes: thread <-> fixed channel vector, two pixels in flight per iteration (loads of both
+// issued before any use) so that ~48-96 B per thread are outstanding -- what HBM3e needs.
+#define HN_COL_LOOP2(it, P)                                                        \
+  for (long long pix = (it).pix0; pix < (P); pix += 2 * (it).pstride)
+__global__ void __launch_bounds__(256) bn_stats_kernel(const bf16* __restrict__ x, long long P, int C, int ld,
+                                                       float* __restrict__ sum, float* __restrict__ sq) {
   extern __shared__ float s_acc[];   // [2][C]
   const int CV = C / 8;
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_acc[i] = 0.f;
   __syncthreads();
   float ps[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  long long total = P * CV;
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int cv = (int)(i0 % CV);
-  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
-    float f[8];
-    load8(x + (i / CV) * ld + cv * 8, f);
+  const ColIter it = col_iter(CV);
+  HN_COL_LOOP2(it, P) {
+    const long long pix2 = pix + it.pstride;
+    const bool two = pix2 < P;
+    float f[8], h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    load8(x + pix * ld + it.cv * 8, f);
+    if (two) load8(x + pix2 * ld + it.cv * 8, h);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { ps[j] += f[j]; pq[j] += f[j] * f[j]; }
+    for (int j = 0; j < 8; ++j) { ps[j] += f[j] + h[j]; pq[j] += f[j] * f[j] + h[j] * h[j]; }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    atomicAdd(&s_acc[cv * 8 + j], ps[j]);
-    atomicAdd(&s_acc[C + cv * 8 + j], pq[j]);
-  }
+  col_fold8(s_acc, ps, it.cv, CV);
+  col_fold8(s_acc + C, pq, it.cv, CV);
   __syncthreads();
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     atomicAdd(sum + i, s_acc[i]);
@@ -145,107 +147,147 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
     rvar[c] = (1.f - momentum) * rvar[c] + momentum * (float)unb;
   }
 }
-__global__ void bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res, bf16* __restrict__ y,
-                                const float* __restrict__ mean, const float* __restrict__ rstd,
-                                const float* __restrict__ gamma, const float* __restrict__ beta, long long P, int C,
-                                int ldx, int ldr, int ldy, int act) {
+__global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
+                                                       bf16* __restrict__ y, const float* __restrict__ mean,
+                                                       const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                       const float* __restrict__ beta, long long P, int C, int ldx,
+                                                       int ldr, int ldy, int act) {
   const int CV = C / 8;
-  long long total = P * CV;
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int cv = (int)(i0 % CV);
+  const ColIter it = col_iter(CV);
   float sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    int c = cv * 8 + j;
+    int c = it.cv * 8 + j;
     sc[j] = rstd[c] * gamma[c];
     sh[j] = beta[c] - mean[c] * sc[j];
   }
-  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
-    long long pix = i / CV;
-    float f[8], r[8];
-    load8(x + pix * ldx + cv * 8, f);
-    if (res) load8(res + pix * ldr + cv * 8, r);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float v = f[j] * sc[j] + sh[j];
-      if (res) v += r[j];
-      f[j] = apply_act(v, act);
+  HN_COL_LOOP2(it, P) {
+    const long long pix2 = pix + it.pstride;
+    const bool two = pix2 < P;
+    float f[2][8], r[2][8];
+    load8(x + pix * ldx + it.cv * 8, f[0]);
+    if (two) load8(x + pix2 * ldx + it.cv * 8, f[1]);
+    if (res) {
+      load8(res + pix * ldr + it.cv * 8, r[0]);
+      if (two) load8(res + pix2 * ldr + it.cv * 8, r[1]);
     }
-    store8(y + pix * ldy + cv * 8, f);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = fmaf(f[u][j], sc[j], sh[j]);
+        if (res) v += r[u][j];
+        f[u][j] = apply_act(v, act);
+      }
+      store8(y + (u ? pix2 : pix) * ldy + it.cv * 8, f[u]);
+    }
   }
 }
-__global__ void bn_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ x,
-                                     bf16* __restrict__ dz, const float* __restrict__ mean, const float* __restrict__ rstd,
-                                     long long P, int C, int lddy, int ldy, int ldx, int lddz, int act,
-                                     float* __restrict__ s1, float* __restrict__ s2) {
+// MASKZ: act is ReLU without residual and the mask is re-derived from x exactly as bn_apply computed
+// y (same fp32 expression), so neither y is read nor dz written: 2 passes instead of 4.
+template <bool MASKZ>
+__global__ void __launch_bounds__(256, 3) bn_bwd_reduce_kernel(
+    const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ x, bf16* __restrict__ dz,
+    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
+    const float* __restrict__ beta, long long P, int C, int lddy, int ldy, int ldx, int lddz, int act,
+    float* __restrict__ s1, float* __restrict__ s2) {
   extern __shared__ float s_acc[];   // [2][C]
   const int CV = C / 8;
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_acc[i] = 0.f;
   __syncthreads();
-  long long total = P * CV;
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int cv = (int)(i0 % CV);
-  float mu[8], rs[8], p1[8], p2[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) { mu[j] = mean[cv * 8 + j]; rs[j] = rstd[cv * 8 + j]; p1[j] = p2[j] = 0.f; }
-  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
-    long long pix = i / CV;
-    float g[8], a[8], f[8];
-    load8(dy + pix * lddy + cv * 8, g);
-    if (act != HN_ACT_NONE) load8(y + pix * ldy + cv * 8, a);
-    load8(x + pix * ldx + cv * 8, f);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float v = g[j];
-      if (act == HN_ACT_RELU) v = a[j] > 0.f ? v : 0.f;
-      else if (act == HN_ACT_SIGMOID) v = v * a[j] * (1.f - a[j]);
-      g[j] = v;
-      float vr = bf16_round(v);
-      p1[j] += vr;
-      p2[j] += vr * (f[j] - mu[j]) * rs[j];
-    }
-    if (dz) store8(dz + pix * lddz + cv * 8, g);
-  }
+  const ColIter it = col_iter(CV);
+  float mu[8], sc[8], sh[8], p1[8], p2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    atomicAdd(&s_acc[cv * 8 + j], p1[j]);
-    atomicAdd(&s_acc[C + cv * 8 + j], p2[j]);
+    int c = it.cv * 8 + j;
+    mu[j] = mean[c]; p1[j] = p2[j] = 0.f;
+    if (MASKZ) { sc[j] = rstd[c] * gamma[c]; sh[j] = beta[c] - mu[j] * sc[j]; }
   }
+  HN_COL_LOOP2(it, P) {
+    const long long pix2 = pix + it.pstride;
+    const bool two = pix2 < P;
+    float g[2][8], a[2][8], f[2][8];
+    load8(dy + pix * lddy + it.cv * 8, g[0]);
+    load8(x + pix * ldx + it.cv * 8, f[0]);
+    if (two) {
+      load8(dy + pix2 * lddy + it.cv * 8, g[1]);
+      load8(x + pix2 * ldx + it.cv * 8, f[1]);
+    }
+    if (!MASKZ && act != HN_ACT_NONE) {
+      load8(y + pix * ldy + it.cv * 8, a[0]);
+      if (two) load8(y + pix2 * ldy + it.cv * 8, a[1]);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = g[u][j];
+        if (MASKZ) v = fmaf(f[u][j], sc[j], sh[j]) > 0.f ? v : 0.f;
+        else if (act == HN_ACT_RELU) v = a[u][j] > 0.f ? v : 0.f;
+        else if (act == HN_ACT_SIGMOID) v = v * a[u][j] * (1.f - a[u][j]);
+        g[u][j] = v;
+        float vr = MASKZ ? v : bf16_round(v);
+        p1[j] += vr;
+        p2[j] += vr * (f[u][j] - mu[j]);
+      }
+      if (!MASKZ && dz) store8(dz + (u ? pix2 : pix) * lddz + it.cv * 8, g[u]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) p2[j] *= rstd[it.cv * 8 + j];
+  col_fold8(s_acc, p1, it.cv, CV);
+  col_fold8(s_acc + C, p2, it.cv, CV);
   __syncthreads();
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     atomicAdd(s1 + i, s_acc[i]);
     atomicAdd(s2 + i, s_acc[C + i]);
   }
 }
-__global__ void bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, bf16* __restrict__ dx,
-                                    const float* __restrict__ mean, const float* __restrict__ rstd,
-                                    const float* __restrict__ gamma, const float* __restrict__ s1,
-                                    const float* __restrict__ s2, long long P, int C, int lddz, int ldx, int lddx,
-                                    int training) {
+template <bool MASKZ>
+__global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(
+    const bf16* __restrict__ dz, const bf16* __restrict__ x, bf16* __restrict__ dx, const float* __restrict__ mean,
+    const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
+    const float* __restrict__ s1, const float* __restrict__ s2, long long P, int C, int lddz, int ldx, int lddx,
+    int training) {
   const int CV = C / 8;
-  long long total = P * CV;
-  long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int cv = (int)(i0 % CV);
-  float mu[8], rs[8], k[8], m1[8], m2[8];
+  const ColIter it = col_iter(CV);
+  // dx = k*(v - m1 - xhat*m2) = k*v + ca + cb*x with per-channel constants
+  float k[8], ca[8], cb[8], sh[8];
   const float invP = 1.f / (float)P;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    int c = cv * 8 + j;
-    mu[j] = mean[c]; rs[j] = rstd[c]; k[j] = gamma[c] * rstd[c];
-    m1[j] = training ? s1[c] * invP : 0.f;
-    m2[j] = training ? s2[c] * invP : 0.f;
+    int c = it.cv * 8 + j;
+    const float mu = mean[c], rs = rstd[c];
+    k[j] = rs * gamma[c];
+    const float m1 = training ? s1[c] * invP : 0.f;
+    const float m2 = training ? s2[c] * invP : 0.f;
+    cb[j] = -k[j] * rs * m2;
+    ca[j] = -k[j] * m1 - cb[j] * mu;
+    if (MASKZ) sh[j] = beta[c] - mu * k[j];
   }
-  for (long long i = i0; i < total; i += (long long)gridDim.x * blockDim.x) {
-    long long pix = i / CV;
-    float g[8], f[8];
-    load8(dz + pix * lddz + cv * 8, g);
-    load8(x + pix * ldx + cv * 8, f);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float xh = (f[j] - mu[j]) * rs[j];
-      f[j] = k[j] * (g[j] - m1[j] - xh * m2[j]);
+  HN_COL_LOOP2(it, P) {
+    const long long pix2 = pix + it.pstride;
+    const bool two = pix2 < P;
+    float g[2][8], f[2][8];
+    load8(dz + pix * lddz + it.cv * 8, g[0]);
+    load8(x + pix * ldx + it.cv * 8, f[0]);
+    if (two) {
+      load8(dz + pix2 * lddz + it.cv * 8, g[1]);
+      load8(x + pix2 * ldx + it.cv * 8, f[1]);
     }
-    store8(dx + pix * lddx + cv * 8, f);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v = g[u][j];
+        if (MASKZ) v = fmaf(f[u][j], k[j], sh[j]) > 0.f ? v : 0.f;
+        f[u][j] = fmaf(k[j], v, fmaf(cb[j], f[u][j], ca[j]));
+      }
+      store8(dx + (u ? pix2 : pix) * lddx + it.cv * 8, f[u]);
+    }
   }
 }
 }  // namespace
@@ -292,14 +334,28 @@ extern "C" int hn_bn_apply(const void* x, const void* res, void* y, const float*
 extern "C" int hn_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, const float* mean, const float* rstd, long long P, int C, int lddy, int ldy, int ldx, int lddz, int act, float* s1, float* s2, void* stream) {
   REQ_CV(C, "bn_bwd_reduce");
   HN_REQUIRE(dy && x && mean && rstd && s1 && s2 && (act == HN_ACT_NONE || y), "bn_bwd_reduce: null");
-  bn_bwd_reduce_kernel<<<grid_for(P * (C / 8)), TPB, 2 * C * sizeof(float), ST>>>((const bf16*)dy, (const bf16*)y, (const bf16*)x, (bf16*)dz, mean, rstd, P, C, lddy, ldy, ldx, lddz, act, s1, s2);
+  bn_bwd_reduce_kernel<false><<<grid_for(P * (C / 8)), TPB, 2 * C * sizeof(float), ST>>>((const bf16*)dy, (const bf16*)y, (const bf16*)x, (bf16*)dz, mean, rstd, nullptr, nullptr, P, C, lddy, ldy, ldx, lddz, act, s1, s2);
   HN_CHECK_LAUNCH("bn_bwd_reduce");
   return HN_OK;
 }
 extern "C" int hn_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* mean, const float* rstd, const float* gamma, const float* s1, const float* s2, long long P, int C, int lddz, int ldx, int lddx, int training, void* stream) {
   REQ_CV(C, "bn_bwd_apply");
   HN_REQUIRE(dz && x && dx && mean && rstd && gamma && s1 && s2, "bn_bwd_apply: null");
-  bn_bwd_apply_kernel<<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)dz, (const bf16*)x, (bf16*)dx, mean, rstd, gamma, s1, s2, P, C, lddz, ldx, lddx, training);
+  bn_bwd_apply_kernel<false><<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)dz, (const bf16*)x, (bf16*)dx, mean, rstd, gamma, nullptr, s1, s2, P, C, lddz, ldx, lddx, training);
   HN_CHECK_LAUNCH("bn_bwd_apply");
+  return HN_OK;
+}
+extern "C" int hn_bn_relu_bwd_reduce(const void* dy, const void* x, const float* mean, const float* rstd, const float* gamma, const float* beta, long long P, int C, int lddy, int ldx, float* s1, float* s2, void* stream) {
+  REQ_CV(C, "bn_relu_bwd_reduce");
+  HN_REQUIRE(dy && x && mean && rstd && gamma && beta && s1 && s2, "bn_relu_bwd_reduce: null");
+  bn_bwd_reduce_kernel<true><<<grid_for(P * (C / 8)), TPB, 2 * C * sizeof(float), ST>>>((const bf16*)dy, nullptr, (const bf16*)x, nullptr, mean, rstd, gamma, beta, P, C, lddy, 0, ldx, 0, HN_ACT_RELU, s1, s2);
+  HN_CHECK_LAUNCH("bn_relu_bwd_reduce");
+  return HN_OK;
+}
+extern "C" int hn_bn_relu_bwd_apply(const void* dy, const void* x, void* dx, const float* mean, const float* rstd, const float* gamma, const float* beta, const float* s1, const float* s2, long long P, int C, int lddy, int ldx, int lddx, int training, void* stream) {
+  REQ_CV(C, "bn_relu_bwd_apply");
+  HN_REQUIRE(dy && x && dx && mean && rstd && gamma && beta && s1 && s2, "bn_relu_bwd_apply: null");
+  bn_bwd_apply_kernel<true><<<grid_for(P * (C / 8)), TPB, 0, ST>>>((const bf16*)dy, (const bf16*)x, (bf16*)dx, mean, rstd, gamma, beta, s1, s2, P, C, lddy, ldx, lddx, training);
+  HN_CHECK_LAUNCH("bn_relu_bwd_apply");
   return HN_OK;
 }

@@ -454,17 +454,28 @@ class _BnActFn(torch.autograd.Function):
         call("hn_bn_apply", z.data_ptr(), _ptr(res), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gam.data_ptr(),
              bet.data_ptr(), P, Cp, ldz, ldr, Cp, act, _stream())
         ctx.act, ctx.training, ctx.C, ctx.has_res = act, training, C, res is not None
-        ctx.save_for_backward(z, y if act != ACT_NONE else None, mean, rstd, gam)
+        ctx.maskz = act == ACT_RELU and res is None      # ReLU mask re-derived from z in backward
+        ctx.save_for_backward(z, y if (act != ACT_NONE and not ctx.maskz) else None, mean, rstd, gam,
+                              bet if ctx.maskz else None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        z, y, mean, rstd, gam = ctx.saved_tensors
+        z, y, mean, rstd, gam, bet = ctx.saved_tensors
         dy, lddy = nhwc(dy)
         z, ldz = nhwc(z)
         B, H, W, Cp = z.shape
         P = B * H * W
         s1, s2 = _f32(Cp, z), _f32(Cp, z)
+        if ctx.maskz:
+            call("hn_bn_relu_bwd_reduce", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                 gam.data_ptr(), bet.data_ptr(), P, Cp, lddy, ldz, s1.data_ptr(), s2.data_ptr(), _stream())
+            dx = _new(B, H, W, Cp, z)
+            call("hn_bn_relu_bwd_apply", dy.data_ptr(), z.data_ptr(), dx.data_ptr(), mean.data_ptr(),
+                 rstd.data_ptr(), gam.data_ptr(), bet.data_ptr(), s1.data_ptr(), s2.data_ptr(), P, Cp, lddy, ldz,
+                 Cp, 1 if ctx.training else 0, _stream())
+            C = ctx.C
+            return (dx, s2[:C].clone(), s1[:C].clone(), None, None, None, None, None, None, None, None, None)
         need_dz_buf = ctx.act != ACT_NONE
         dz = _new(B, H, W, Cp, z) if need_dz_buf else dy
         lddz = Cp if need_dz_buf else lddy
@@ -510,10 +521,12 @@ class _ConvStatsFn(torch.autograd.Function):
         x1, x2, weight = ctx.saved_tensors
         g = ctx.g
         need = ctx.needs_input_grad
-        dz, dbias = _act_bwd(dy, None, ACT_NONE, ctx.has_bias and need[3])
+        # a bias in front of train-mode BatchNorm has an exactly-zero gradient: dy here is the BN input
+        # gradient, whose per-channel sum vanishes identically (sum_p [dz - mean(dz) - xhat*mean(dz*xhat)]
+        # = 0); the reference's autograd gets fp32 round-off around 0.  No reduction pass is spent on it.
+        dz, _ = _act_bwd(dy, None, ACT_NONE, False)
+        dbias = torch.zeros(g.Cout, dtype=torch.float32, device=dz.device) if (ctx.has_bias and need[3]) else None
         dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2])
-        if dbias is not None:
-            dbias = dbias[: g.Cout]
         return (dx1 if need[0] else None, dx2 if need[1] else None, dw, dbias, None, None, None, None, None)
 
 
