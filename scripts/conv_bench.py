@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--only", default="")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--wgrad", action="store_true")
+    ap.add_argument("--nostats", action="store_true")
     a = ap.parse_args()
     lib = _lib.load()
     dev = torch.device("cuda")
@@ -43,6 +44,7 @@ def main():
         if a.only and a.only not in tag:
             continue
         OH, OW = H // s, W // s
+        st = st and not a.nostats
         n = 4 * pshuf if pshuf else Cout
         pad = 0 if (k == 1 or s == 2) else dil
         Kpad = lib.hn_conv_kpad(k, k, C1 + C2)

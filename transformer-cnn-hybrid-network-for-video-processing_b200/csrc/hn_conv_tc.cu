@@ -20,14 +20,15 @@
 namespace {
 
 constexpr int BM = 128;
-constexpr int BKC = 64;                      // channels per K step (128 bytes)
-constexpr int A_BYTES = BM * BKC * 2;        // 16 KB
+// BKC = channels per K step: 64 (128-byte rows, SWIZZLE_128B) or 32 (64-byte rows, SWIZZLE_64B; the
+// C = 32 layers of UNet level 1)
 constexpr int NTHREADS_TC = 192;
+constexpr int STAT_MAX = 2048;               // channels whose BN statistics one CTA can hold
 
 struct TcParams {
   int B, H, W;
   int C1, C2, Cout, Ntot, ldy;
-  int KH, KW, pad, dil;
+  int KH, KW, pad, dil, es;
   int BW, BH, BB, tiles_w, tiles_h;
   int m_tiles, n_tiles, kiters_per_tap1, kiters_per_tap2;
   int act, pshuf;
@@ -101,14 +102,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
-// SW128 K-major shared-memory matrix descriptor (rows of 128 B, 8-row groups 1024 B apart)
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+// K-major swizzled shared-memory matrix descriptor: rows of ROWB bytes (128 -> SWIZZLE_128B, 64 ->
+// SWIZZLE_64B), 8-row groups 8*ROWB bytes apart
+template <int ROWB>
+__device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t smem_addr) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);       // start address
   d |= (uint64_t)1 << 16;                             // leading byte offset (unused for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;                   // stride byte offset
+  d |= (uint64_t)((8 * ROWB) >> 4) << 32;             // stride byte offset
   d |= (uint64_t)1 << 46;                             // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;                             // SWIZZLE_128B
+  d |= (uint64_t)(ROWB == 128 ? 2 : 4) << 61;         // SWIZZLE_128B / SWIZZLE_64B
   return d;
 }
 // column sums of a 32(row=lane) x 32(col=register) block: after the butterfly lane j holds column j
@@ -126,13 +129,14 @@ __device__ __forceinline__ float colsum32(float* v, int lane) {
   return v[0];
 }
 
-template <int BN>
+template <int BN, int BKC>
 __global__ void __launch_bounds__(NTHREADS_TC, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapB, const TcParams p) {
+  constexpr int A_BYTES = BM * BKC * 2;
   constexpr int B_BYTES = BN * BKC * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 8 ? 8 : (200 * 1024 / STAGE_BYTES);
+  constexpr int STAGES = (192 * 1024 / STAGE_BYTES) > 8 ? 8 : (192 * 1024 / STAGE_BYTES);
   constexpr int ACC_STRIDE = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
   constexpr int TMEM_COLS = 2 * ACC_STRIDE;
   constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
@@ -141,6 +145,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   __shared__ __align__(8) uint64_t bars[2 * 8 + 4];
   __shared__ uint32_t tmem_base_slot;
+  // BatchNorm sum / sum-of-squares are accumulated per CTA here and flushed with ONE global atomic per
+  // channel per CTA at the end (per-tile global atomics serialise on the same few addresses in L2)
+  __shared__ float s_stat[2][STAT_MAX];
+  if (p.ssum) {
+    for (int i = threadIdx.x; i < 2 * STAT_MAX; i += NTHREADS_TC) (&s_stat[0][0])[i] = 0.f;
+  }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[8]);
@@ -177,7 +187,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
         const int w0 = tw * p.BW, h0 = th * p.BH, b0 = tb * p.BB, n0 = nt * BN;
         for (int tap = 0; tap < taps; ++tap) {
           const int kh = tap / p.KW, kw = tap - kh * p.KW;
-          const int hh = h0 + kh * p.dil - p.pad, ww = w0 + kw * p.dil - p.pad;
+          const int hh = h0 * p.es + kh * p.dil - p.pad, ww = w0 * p.es + kw * p.dil - p.pad;
           for (int kc = 0; kc < kit_tap; ++kc) {
             mbar_wait(empty0 + 8 * stage, phase ^ 1);
             const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
@@ -205,7 +215,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           mbar_wait(full0 + 8 * stage, phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-          const uint64_t da = make_sw128_desc(sa), db = make_sw128_desc(sa + A_BYTES);
+          const uint64_t da = make_kmajor_desc<BKC * 2>(sa), db = make_kmajor_desc<BKC * 2>(sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BKC / 16; ++k)
             umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (kit > 0 || k > 0) ? 1u : 0u);
@@ -266,8 +276,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) { float q = bf16_round(v[j]); t[j] = q * q; }
           float q = colsum32(t, lane);
-          atomicAdd(p.ssum + ch0 + lane, s);
-          atomicAdd(p.ssq + ch0 + lane, q);
+          atomicAdd(&s_stat[0][ch0 + lane], s);
+          atomicAdd(&s_stat[1][ch0 + lane], q);
         }
         bf16* dst = p.y + pix * p.ldy + ch0;
 #pragma unroll
@@ -281,6 +291,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+    }
+    if (p.ssum) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");            // the four epilogue warps only
+      const int nstat = p.pshuf ? p.pshuf : p.Ntot;
+      for (int i = threadIdx.x - 64; i < nstat; i += 128) {
+        const float a = s_stat[0][i], b = s_stat[1][i];
+        if (a != 0.f || b != 0.f) { atomicAdd(p.ssum + i, a); atomicAdd(p.ssq + i, b); }
+      }
     }
   }
   tc_fence_before();
@@ -325,54 +343,63 @@ int pick_bn(int ntot) {
     if (ntot % c == 0) return c;
   return 0;
 }
+int pick_bkc(const HnConv* d) {
+  if (d->C1 % 64 == 0 && d->C2 % 64 == 0) return 64;
+  if (d->C1 % 32 == 0 && d->C2 % 32 == 0) return 32;
+  return 0;
+}
 bool tc_ok(const HnConv* d) {
-  if (!d || d->mode != 0 || d->stride != 1 || d->ups != 0) return false;
-  if (d->C1 <= 0 || d->C1 % 64 || d->C2 % 64) return false;
-  if (d->OH != d->H || d->OW != d->W) return false;
-  if (d->pshuf && (d->KH != 1 || d->KW != 1 || d->pshuf % 32)) return false;
+  if (!d || d->mode != 0 || d->ups != 0) return false;
+  if (d->stride != 1 && d->stride != 2) return false;
+  if (d->C1 <= 0 || pick_bkc(d) == 0) return false;
+  if (d->H % d->stride || d->W % d->stride || d->OH != d->H / d->stride || d->OW != d->W / d->stride) return false;
+  if (d->pshuf && (d->KH != 1 || d->KW != 1 || d->pshuf % 32 || d->stride != 1)) return false;
   int ntot = d->pshuf ? 4 * d->pshuf : d->Cout;
-  if (pick_bn(ntot) == 0 || ntot < 64) return false;
+  if (pick_bn(ntot) == 0) return false;
+  if (pick_bkc(d) == 32 && pick_bn(ntot) > 64) return false;      // BKC = 32 is built for BN in {32, 64}
   if (d->ldy % 8 || d->ld1 % 8 || (d->C2 && d->ld2 % 8)) return false;
-  if ((long long)d->B * d->H * d->W % 128) return false;
+  if ((long long)d->B * d->OH * d->OW % 128) return false;
   TileGeom g;
-  return tile_geom(d->B, d->H, d->W, &g) && get_encode() != nullptr;
+  if (!tile_geom(d->B, d->OH, d->OW, &g)) return false;
+  if (g.BW * d->stride > 256 || g.BH * d->stride > 256) return false;
+  return get_encode() != nullptr;
 }
 
-int make_map_act(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int ld, const TileGeom& g) {
+int make_map_act(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int ld, const TileGeom& g, int es, int bkc) {
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)W * ld * 2, (cuuint64_t)H * W * ld * 2};
-  cuuint32_t box[4] = {64, (cuuint32_t)g.BW, (cuuint32_t)g.BH, (cuuint32_t)g.BB};
-  cuuint32_t es[4] = {1, 1, 1, 1};
-  CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
-                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  cuuint32_t box[4] = {(cuuint32_t)bkc, (cuuint32_t)(g.BW * es), (cuuint32_t)(g.BH * es), (cuuint32_t)g.BB};
+  cuuint32_t estr[4] = {1, (cuuint32_t)es, (cuuint32_t)es, 1};
+  CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, bkc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : (int)r;
 }
-int make_map_w(CUtensorMap* m, const void* ptr, int Npad, int Kpad, int BN) {
+int make_map_w(CUtensorMap* m, const void* ptr, int Npad, int Kpad, int BN, int bkc) {
   cuuint64_t dims[2] = {(cuuint64_t)Kpad, (cuuint64_t)Npad};
   cuuint64_t strides[1] = {(cuuint64_t)Kpad * 2};
-  cuuint32_t box[2] = {64, (cuuint32_t)BN};
+  cuuint32_t box[2] = {(cuuint32_t)bkc, (cuuint32_t)BN};
   cuuint32_t es[2] = {1, 1};
   CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
-                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, bkc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
-template <int BN>
+template <int BN, int BKC>
 int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& bm, const TcParams& p, cudaStream_t st) {
-  constexpr int STAGE_BYTES = A_BYTES + BN * BKC * 2;
-  constexpr int STAGES = (200 * 1024 / STAGE_BYTES) > 8 ? 8 : (200 * 1024 / STAGE_BYTES);
+  constexpr int STAGE_BYTES = BM * BKC * 2 + BN * BKC * 2;
+  constexpr int STAGES = (192 * 1024 / STAGE_BYTES) > 8 ? 8 : (192 * 1024 / STAGE_BYTES);
   constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "conv_tc: smem attribute: %s", cudaGetErrorString(e));
     configured = true;
   }
   int tiles = p.m_tiles * p.n_tiles;
   int grid = tiles < 148 ? tiles : 148;
-  conv_tc_kernel<BN><<<grid, NTHREADS_TC, SMEM, st>>>(a1, a2, bm, p);
+  conv_tc_kernel<BN, BKC><<<grid, NTHREADS_TC, SMEM, st>>>(a1, a2, bm, p);
   HN_CHECK_LAUNCH("conv_tc_kernel");
   return HN_OK;
 }
@@ -386,39 +413,42 @@ extern "C" int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, c
   HN_REQUIRE(tc_ok(d), "conv_tc_fwd: geometry not supported by the tcgen05 path (use hn_conv2d_fwd)");
   HN_REQUIRE(x1 && wpacked && y && (d->C2 == 0 || x2), "conv_tc_fwd: null pointer");
   HN_REQUIRE((stat_sum == nullptr) == (stat_sqsum == nullptr), "conv_tc_fwd: stats need both buffers");
+  HN_REQUIRE(stat_sum == nullptr || (d->pshuf ? d->pshuf : d->Cout) <= STAT_MAX, "conv_tc_fwd: too many channels for fused statistics");
   HN_REQUIRE(((uintptr_t)x1 % 16) == 0 && ((uintptr_t)wpacked % 16) == 0 && ((uintptr_t)y % 16) == 0, "conv_tc_fwd: 16B alignment");
   TileGeom g;
-  tile_geom(d->B, d->H, d->W, &g);
+  tile_geom(d->B, d->OH, d->OW, &g);
   const int ntot = d->pshuf ? 4 * d->pshuf : d->Cout;
   const int BN = pick_bn(ntot);
+  const int bkc = pick_bkc(d);
   const int Cin = d->C1 + d->C2;
   HN_REQUIRE(d->Kpad == d->KH * d->KW * Cin, "conv_tc_fwd: Kpad mismatch");
   CUtensorMap a1, a2, bm;
-  int rc = make_map_act(&a1, x1, d->B, d->H, d->W, d->C1, d->ld1, g);
+  int rc = make_map_act(&a1, x1, d->B, d->H, d->W, d->C1, d->ld1, g, d->stride, bkc);
   if (rc) HN_FAIL(HN_ECUDA, "conv_tc_fwd: cuTensorMapEncodeTiled(A1) = %d", rc);
   if (d->C2) {
-    rc = make_map_act(&a2, x2, d->B, d->H, d->W, d->C2, d->ld2, g);
+    rc = make_map_act(&a2, x2, d->B, d->H, d->W, d->C2, d->ld2, g, d->stride, bkc);
     if (rc) HN_FAIL(HN_ECUDA, "conv_tc_fwd: cuTensorMapEncodeTiled(A2) = %d", rc);
   } else {
     a2 = a1;
   }
-  rc = make_map_w(&bm, wpacked, hn_conv_npad(ntot), d->Kpad, BN);
+  rc = make_map_w(&bm, wpacked, hn_conv_npad(ntot), d->Kpad, BN, bkc);
   if (rc) HN_FAIL(HN_ECUDA, "conv_tc_fwd: cuTensorMapEncodeTiled(B) = %d", rc);
   TcParams p;
-  p.B = d->B; p.H = d->H; p.W = d->W; p.C1 = d->C1; p.C2 = d->C2; p.Cout = d->Cout; p.Ntot = ntot; p.ldy = d->ldy;
-  p.KH = d->KH; p.KW = d->KW; p.pad = d->pad; p.dil = d->dil;
-  p.BW = g.BW; p.BH = g.BH; p.BB = g.BB; p.tiles_w = d->W / g.BW; p.tiles_h = d->H / g.BH;
-  p.m_tiles = (int)((long long)d->B * d->H * d->W / 128);
+  p.B = d->B; p.H = d->OH; p.W = d->OW; p.C1 = d->C1; p.C2 = d->C2; p.Cout = d->Cout; p.Ntot = ntot; p.ldy = d->ldy;
+  p.KH = d->KH; p.KW = d->KW; p.pad = d->pad; p.dil = d->dil; p.es = d->stride;
+  p.BW = g.BW; p.BH = g.BH; p.BB = g.BB; p.tiles_w = d->OW / g.BW; p.tiles_h = d->OH / g.BH;
+  p.m_tiles = (int)((long long)d->B * d->OH * d->OW / 128);
   p.n_tiles = ntot / BN;
-  p.kiters_per_tap1 = d->C1 / 64; p.kiters_per_tap2 = d->C2 / 64;
+  p.kiters_per_tap1 = d->C1 / bkc; p.kiters_per_tap2 = d->C2 / bkc;
   p.act = d->act; p.pshuf = d->pshuf; p.bias = bias; p.y = (bf16*)y; p.ssum = stat_sum; p.ssq = stat_sqsum;
   cudaStream_t st = (cudaStream_t)stream;
+  if (bkc == 32) return BN == 64 ? launch_tc<64, 32>(a1, a2, bm, p, st) : launch_tc<32, 32>(a1, a2, bm, p, st);
   switch (BN) {
-    case 256: return launch_tc<256>(a1, a2, bm, p, st);
-    case 192: return launch_tc<192>(a1, a2, bm, p, st);
-    case 128: return launch_tc<128>(a1, a2, bm, p, st);
-    case 96: return launch_tc<96>(a1, a2, bm, p, st);
-    case 64: return launch_tc<64>(a1, a2, bm, p, st);
-    default: return launch_tc<32>(a1, a2, bm, p, st);
+    case 256: return launch_tc<256, 64>(a1, a2, bm, p, st);
+    case 192: return launch_tc<192, 64>(a1, a2, bm, p, st);
+    case 128: return launch_tc<128, 64>(a1, a2, bm, p, st);
+    case 96: return launch_tc<96, 64>(a1, a2, bm, p, st);
+    case 64: return launch_tc<64, 64>(a1, a2, bm, p, st);
+    default: return launch_tc<32, 64>(a1, a2, bm, p, st);
   }
 }
