@@ -19,14 +19,14 @@ namespace {
 constexpr int PK = 64;                       // pixels per stage
 constexpr int BOX_BYTES = PK * 128;          // one {64 ch, 64 px} box
 constexpr int MAX_BOXES = 8;                 // 2 m-tiles x 2 + 4 n-boxes
-constexpr int WG_STAGES = 3;
+constexpr int WG_STAGES = 8;                 // upper bound; the launch uses as many as fit in 192 KB
 constexpr int WG_THREADS = 192;
 
 struct WgTc {
   int Cout, C1, C2, Creal;
   int KH, KW, pad, dil, es;
   int BW, BH, BB, tiles_w, tiles_h;
-  int ptiles, splits, tiles_per_split;
+  int ptiles, splits, tiles_per_split, stages;
   int mblocks, ct1, ct2;                    // n-blocks of 256, c-tiles (<=256) in x1 / x2
   long long s_n, s_c, s_kh, s_kw;
   float* dw;
@@ -121,13 +121,16 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
   const int nboxes = ncols / 64;
   const int n_off = mb * 256;
   const int mtiles = min(2, (p.Cout - n_off + 127) / 128);
-  const int aboxes = mtiles * 2;
+  // dz boxes actually fetched: 64-channel blocks that exist (a missing upper half of an m-tile aliases the
+  // lower one through LBO = 0; its accumulator lanes are never read back)
+  const int aboxes = min(mtiles * 2, (p.Cout - n_off + 63) / 64);
   const int stage_bytes = (aboxes + nboxes) * BOX_BYTES;
+  const int nstages = p.stages;
   const int t0 = split * p.tiles_per_split, t1 = min(p.ptiles, t0 + p.tiles_per_split);
   const int kh = tap / p.KW, kw = tap - kh * p.KW;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < WG_STAGES; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+    for (int s = 0; s < nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
     mbar_init(done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -149,13 +152,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
         const int tw = t % p.tiles_w, th = (t / p.tiles_w) % p.tiles_h, tb = t / (p.tiles_w * p.tiles_h);
         const int w0 = tw * p.BW, h0 = th * p.BH, b0 = tb * p.BB;
         mbar_wait(empty0 + 8 * stage, phase ^ 1);
-        const uint32_t sa = smem_u32(smem + stage * (MAX_BOXES * BOX_BYTES));
+        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
         mbar_arrive_expect_tx(full0 + 8 * stage, stage_bytes);
         for (int i = 0; i < aboxes; ++i) tma_load_4d(sa + i * BOX_BYTES, &mapDZ, full0 + 8 * stage, n_off + i * 64, w0, h0, b0);
         const int xw = w0 * p.es + kw * p.dil - p.pad, xh = h0 * p.es + kh * p.dil - p.pad;
         for (int i = 0; i < nboxes; ++i)
           tma_load_4d(sa + (aboxes + i) * BOX_BYTES, mx, full0 + 8 * stage, c_off + i * 64, xw, xh, b0);
-        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -167,18 +170,18 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
       for (int t = t0; t < t1; ++t) {
         mbar_wait(full0 + 8 * stage, phase);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * (MAX_BOXES * BOX_BYTES));
+        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
         const uint32_t sb = sa + aboxes * BOX_BYTES;
         for (int mt = 0; mt < mtiles; ++mt) {
 #pragma unroll
           for (int k = 0; k < PK / 16; ++k) {
-            const uint64_t da = make_mn_desc(sa + mt * 2 * BOX_BYTES + k * 2048, BOX_BYTES);
+            const uint64_t da = make_mn_desc(sa + mt * 2 * BOX_BYTES + k * 2048, (2 * mt + 1 < aboxes) ? BOX_BYTES : 0);
             const uint64_t db = make_mn_desc(sb + k * 2048, BOX_BYTES);
             umma_bf16(tmem_base + mt * 256, da, db, idesc, (t > t0 || k > 0) ? 1u : 0u);
           }
         }
         umma_commit(empty0 + 8 * stage);
-        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
       umma_commit(done);
     }
@@ -290,13 +293,24 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
   p.ct1 = (d->C1 + 255) / 256; p.ct2 = (d->C2 + 255) / 256;
   p.s_n = s_n; p.s_c = s_c; p.s_kh = s_kh; p.s_kw = s_kw; p.dw = dw;
   const int jobs = p.mblocks * (p.ct1 + p.ct2) * d->KH * d->KW;
-  int splits = (148 * 2 + jobs - 1) / jobs;               // ~2 waves of work items
-  int max_splits = p.ptiles / 8 > 0 ? p.ptiles / 8 : 1;   // at least 8 pixel tiles (512 px) per item
+  // whole waves of 148 CTAs (one CTA per SM: 512 TMEM columns): the largest split count that keeps
+  // jobs * splits <= 2 * 148, at least 8 pixel tiles (512 px) per work item
+  int splits = (148 * 2) / jobs;
+  int max_splits = p.ptiles / 8 > 0 ? p.ptiles / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
   p.tiles_per_split = (p.ptiles + splits - 1) / splits;
   p.splits = (p.ptiles + p.tiles_per_split - 1) / p.tiles_per_split;
-  const int SMEM = WG_STAGES * MAX_BOXES * BOX_BYTES + 1024;
+  // stage = the boxes one pixel step needs (worst case over work items), as many stages as fit in 192 KB
+  {
+    const int rem = d->Cout < 256 ? d->Cout : 256;
+    const int ab = (rem + 63) / 64;
+    const int c1 = d->C1 < 256 ? d->C1 : 256, c2 = d->C2 < 256 ? d->C2 : 256;
+    const int nb = (c1 > c2 ? c1 : c2) / 64;
+    int st = (192 * 1024) / ((ab + nb) * BOX_BYTES);
+    p.stages = st > WG_STAGES ? WG_STAGES : (st < 2 ? 2 : st);
+  }
+  const int SMEM = 192 * 1024 + 1024;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
