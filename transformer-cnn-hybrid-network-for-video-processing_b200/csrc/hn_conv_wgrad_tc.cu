@@ -27,6 +27,7 @@ struct WgTc {
   int KH, KW, pad, dil, es;
   int BW, BH, BB, tiles_w, tiles_h;
   int ptiles, splits, tiles_per_split, stages;
+  int tpj, tgroups;                         // taps per work item, tap groups
   int mblocks, ct1, ct2;                    // n-blocks of 256, c-tiles (<=256) in x1 / x2
   long long s_n, s_c, s_kh, s_kw;
   float* dw;
@@ -111,7 +112,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
   int item = blockIdx.x;
   const int ctiles = p.ct1 + p.ct2, taps = p.KH * p.KW;
   const int ct = item % ctiles; item /= ctiles;
-  const int tap = item % taps; item /= taps;
+  const int tg = item % p.tgroups; item /= p.tgroups;
   const int mb = item % p.mblocks; item /= p.mblocks;
   const int split = item;
   const bool from2 = ct >= p.ct1;
@@ -124,10 +125,11 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
   // dz boxes actually fetched: 64-channel blocks that exist (a missing upper half of an m-tile aliases the
   // lower one through LBO = 0; its accumulator lanes are never read back)
   const int aboxes = min(mtiles * 2, (p.Cout - n_off + 63) / 64);
-  const int stage_bytes = (aboxes + nboxes) * BOX_BYTES;
+  // this item's taps [tap0, tap0 + ntap): each (tap, m-tile) owns ncols TMEM columns, dz is fetched once
+  const int tap0 = tg * p.tpj, ntap = min(p.tpj, taps - tap0);
+  const int stage_bytes = (aboxes + ntap * nboxes) * BOX_BYTES;
   const int nstages = p.stages;
   const int t0 = split * p.tiles_per_split, t1 = min(p.ptiles, t0 + p.tiles_per_split);
-  const int kh = tap / p.KW, kw = tap - kh * p.KW;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < nstages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
@@ -155,9 +157,12 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
         const uint32_t sa = smem_u32(smem + stage * stage_bytes);
         mbar_arrive_expect_tx(full0 + 8 * stage, stage_bytes);
         for (int i = 0; i < aboxes; ++i) tma_load_4d(sa + i * BOX_BYTES, &mapDZ, full0 + 8 * stage, n_off + i * 64, w0, h0, b0);
-        const int xw = w0 * p.es + kw * p.dil - p.pad, xh = h0 * p.es + kh * p.dil - p.pad;
-        for (int i = 0; i < nboxes; ++i)
-          tma_load_4d(sa + (aboxes + i) * BOX_BYTES, mx, full0 + 8 * stage, c_off + i * 64, xw, xh, b0);
+        for (int ti = 0; ti < ntap; ++ti) {
+          const int kh = (tap0 + ti) / p.KW, kw = (tap0 + ti) - kh * p.KW;
+          const int xw = w0 * p.es + kw * p.dil - p.pad, xh = h0 * p.es + kh * p.dil - p.pad;
+          for (int i = 0; i < nboxes; ++i)
+            tma_load_4d(sa + (aboxes + ti * nboxes + i) * BOX_BYTES, mx, full0 + 8 * stage, c_off + i * 64, xw, xh, b0);
+        }
         if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
     }
@@ -171,13 +176,15 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
         mbar_wait(full0 + 8 * stage, phase);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-        const uint32_t sb = sa + aboxes * BOX_BYTES;
-        for (int mt = 0; mt < mtiles; ++mt) {
+        for (int ti = 0; ti < ntap; ++ti) {
+          const uint32_t sb = sa + (aboxes + ti * nboxes) * BOX_BYTES;
+          for (int mt = 0; mt < mtiles; ++mt) {
 #pragma unroll
-          for (int k = 0; k < PK / 16; ++k) {
-            const uint64_t da = make_mn_desc(sa + mt * 2 * BOX_BYTES + k * 2048, (2 * mt + 1 < aboxes) ? BOX_BYTES : 0);
-            const uint64_t db = make_mn_desc(sb + k * 2048, BOX_BYTES);
-            umma_bf16(tmem_base + mt * 256, da, db, idesc, (t > t0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < PK / 16; ++k) {
+              const uint64_t da = make_mn_desc(sa + mt * 2 * BOX_BYTES + k * 2048, (2 * mt + 1 < aboxes) ? BOX_BYTES : 0);
+              const uint64_t db = make_mn_desc(sb + k * 2048, BOX_BYTES);
+              umma_bf16(tmem_base + (ti * mtiles + mt) * ncols, da, db, idesc, (t > t0 || k > 0) ? 1u : 0u);
+            }
           }
         }
         umma_commit(empty0 + 8 * stage);
@@ -190,19 +197,22 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
     mbar_wait(done, 0);
     tc_fence_after();
     if (t1 > t0) {
-      for (int mt = 0; mt < mtiles; ++mt) {
-        const int n = n_off + mt * 128 + lane_base + lane;
-        const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + mt * 256;
-        for (int c = 0; c < ncols / 32; ++c) {
-          uint32_t r[32];
-          tmem_ld32(t_row + c * 32, r);
-          if (n < p.Cout) {
-            const int cg = (from2 ? p.C1 : 0) + c_off + c * 32;
-            float* dst = p.dw + n * p.s_n + kh * p.s_kh + kw * p.s_kw;
+      for (int ti = 0; ti < ntap; ++ti) {
+        const int kh = (tap0 + ti) / p.KW, kw = (tap0 + ti) - kh * p.KW;
+        for (int mt = 0; mt < mtiles; ++mt) {
+          const int n = n_off + mt * 128 + lane_base + lane;
+          const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + (ti * mtiles + mt) * ncols;
+          for (int c = 0; c < ncols / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(t_row + c * 32, r);
+            if (n < p.Cout) {
+              const int cg = (from2 ? p.C1 : 0) + c_off + c * 32;
+              float* dst = p.dw + n * p.s_n + kh * p.s_kh + kw * p.s_kw;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float v = __uint_as_float(r[j]);
-              if (cg + j < p.Creal && v != 0.f) atomicAdd(dst + (cg + j) * p.s_c, v);
+              for (int j = 0; j < 32; ++j) {
+                const float v = __uint_as_float(r[j]);
+                if (cg + j < p.Creal && v != 0.f) atomicAdd(dst + (cg + j) * p.s_c, v);
+              }
             }
           }
         }
@@ -292,7 +302,19 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
   p.mblocks = (d->Cout + 255) / 256;
   p.ct1 = (d->C1 + 255) / 256; p.ct2 = (d->C2 + 255) / 256;
   p.s_n = s_n; p.s_c = s_c; p.s_kh = s_kh; p.s_kw = s_kw; p.dw = dw;
-  const int jobs = p.mblocks * (p.ct1 + p.ct2) * d->KH * d->KW;
+  // taps per work item: as many (tap, m-tile) accumulators of nc_max columns as the 512 TMEM columns hold,
+  // at most 7 boxes of x per stage, balanced over the groups
+  const int taps = d->KH * d->KW;
+  const int mt_max = d->Cout > 128 ? 2 : 1;
+  const int c1m = d->C1 < 256 ? d->C1 : 256, c2m = d->C2 < 256 ? d->C2 : 256;
+  const int nc_max = c1m > c2m ? c1m : c2m;
+  int tpj = 512 / (mt_max * nc_max);
+  if (tpj * (nc_max / 64) > 6) tpj = 6 / (nc_max / 64);
+  if (tpj < 1) tpj = 1;
+  if (tpj > taps) tpj = taps;
+  p.tgroups = (taps + tpj - 1) / tpj;
+  p.tpj = (taps + p.tgroups - 1) / p.tgroups;
+  const int jobs = p.mblocks * (p.ct1 + p.ct2) * p.tgroups;
   // whole waves of 148 CTAs (one CTA per SM: 512 TMEM columns): the largest split count that keeps
   // jobs * splits <= 2 * 148, at least 8 pixel tiles (512 px) per work item
   int splits = (148 * 2) / jobs;
@@ -306,7 +328,7 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
     const int rem = d->Cout < 256 ? d->Cout : 256;
     const int ab = (rem + 63) / 64;
     const int c1 = d->C1 < 256 ? d->C1 : 256, c2 = d->C2 < 256 ? d->C2 : 256;
-    const int nb = (c1 > c2 ? c1 : c2) / 64;
+    const int nb = (c1 > c2 ? c1 : c2) / 64 * p.tpj;
     int st = (192 * 1024) / ((ab + nb) * BOX_BYTES);
     p.stages = st > WG_STAGES ? WG_STAGES : (st < 2 ? 2 : st);
   }
