@@ -121,6 +121,7 @@ def _attn_work(args, bwd):
 WORK = {
     "hn_conv2d_fwd": lambda a: _conv_work(a),
     "hn_conv_tc_fwd": lambda a: _conv_work(a),
+    "hn_conv_sc_fwd": lambda a: _conv_work(a),
     "hn_conv2d_wgrad": lambda a: _conv_work(a),
     "hn_conv_wgrad_tc": lambda a: _conv_work(a),
     "hn_attn_fwd": lambda a: _attn_work(a, False),

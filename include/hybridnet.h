@@ -195,6 +195,15 @@ int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* 
                       const float* bias, void* y, float* stat_sum, float* stat_sqsum,
                       void* stream);
 
+/* ---- small-channel direct convolution (Cin <= 64, Cout <= 64, Cin*Cout <= 2048) -------------- */
+/* Same contract as hn_conv2d_fwd (no residual) for stride-1 "same" 1x1 / 3x3 (dilated) convs on maps
+ * with H % 16 == 0, W % 32 == 0: all of FCT.py:88,110-113,140-143,170-172,194-196,205 and
+ * AutoEncoder.py:9-12,36-38,57-59, UNet.py level 1.  HBM-bound layers: the input halo of a 16x32
+ * tile is staged once in shared memory and the taps are shifted ldmatrix reads of it. */
+int hn_conv_sc_supported(const HnConv* d);
+int hn_conv_sc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
+                   const float* bias, void* y, float* stat_sum, float* stat_sqsum, void* stream);
+
 /* tcgen05 weight gradient: same contract as hn_conv2d_wgrad for stride 1/2 convs with C1%64==0,
  * C2%64==0, Cout>=64 and 64-pixel tileable output maps.  Per tap: D[Cout,Cin] = dz^T x_tap with both
  * operands MN-major straight from TMA boxes, accumulators in TMEM, split over pixels + fp32 atomics. */

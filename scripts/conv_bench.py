@@ -26,6 +26,10 @@ GEOMS = [
     ("un_3x3_512_512", 32, 16, 16, 512, 0, 512, 3, 1, 1, 0, 1),
     ("fct_3x3_8_8", 32, 256, 256, 8, 0, 8, 3, 1, 1, 0, 0),
     ("fct_3x3_16_16", 32, 128, 128, 16, 0, 16, 3, 1, 1, 0, 0),
+    ("fct_3x3_8_8_d3", 32, 128, 128, 8, 0, 8, 3, 1, 3, 0, 0),
+    ("fct_1x1_8_8", 32, 128, 128, 8, 0, 8, 1, 1, 1, 0, 0),
+    ("fct_3x3_32_32", 32, 64, 64, 32, 0, 32, 3, 1, 1, 0, 0),
+    ("fct_3x3_8_1", 32, 256, 256, 8, 0, 1, 3, 1, 1, 0, 0),
 ]
 
 
@@ -53,7 +57,7 @@ def main():
         nbuf = max(2, int(400e6 // byt) + 1)
         xs = [torch.randn(B, H, W, C1, device=dev).bfloat16() for _ in range(nbuf)]
         x2 = [torch.randn(B, H, W, C2, device=dev).bfloat16() for _ in range(nbuf)] if C2 else None
-        oh, ow, oc = (2 * OH, 2 * OW, pshuf) if pshuf else (OH, OW, Cout)
+        oh, ow, oc = (2 * OH, 2 * OW, pshuf) if pshuf else (OH, OW, (Cout + 7) // 8 * 8)
         outs = [torch.empty(B, oh, ow, oc, device=dev, dtype=torch.bfloat16) for _ in range(nbuf)]
         stats = (torch.zeros(max(oc, 8), device=dev), torch.zeros(max(oc, 8), device=dev)) if st else None
         flops = 2.0 * B * OH * OW * n * k * k * (C1 + C2)
