@@ -124,6 +124,7 @@ WORK = {
     "hn_conv_sc_fwd": lambda a: _conv_work(a),
     "hn_conv2d_wgrad": lambda a: _conv_work(a),
     "hn_conv_wgrad_tc": lambda a: _conv_work(a),
+    "hn_conv_wgrad_sc": lambda a: _conv_work(a),
     "hn_attn_fwd": lambda a: _attn_work(a, False),
     "hn_attn_bwd": lambda a: _attn_work(a, True),
 }

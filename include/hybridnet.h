@@ -204,6 +204,12 @@ int hn_conv_sc_supported(const HnConv* d);
 int hn_conv_sc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
                    const float* bias, void* y, float* stat_sum, float* stat_sqsum, void* stream);
 
+/* small-channel weight gradient: same contract as hn_conv2d_wgrad for the hn_conv_sc_fwd geometries */
+int hn_conv_wgrad_sc_supported(const HnConv* d);
+int hn_conv_wgrad_sc(const HnConv* d, const void* x1, const void* x2, const void* dy, float* dw,
+                     int Creal, long long s_n, long long s_c, long long s_kh, long long s_kw,
+                     void* stream);
+
 /* tcgen05 weight gradient: same contract as hn_conv2d_wgrad for stride 1/2 convs with C1%64==0,
  * C2%64==0, Cout>=64 and 64-pixel tileable output maps.  Per tap: D[Cout,Cin] = dz^T x_tap with both
  * operands MN-major straight from TMA boxes, accumulators in TMEM, split over pixels + fp32 atomics. */

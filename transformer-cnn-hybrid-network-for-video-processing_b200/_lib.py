@@ -67,6 +67,8 @@ SIGNATURES = {
     "hn_conv_tc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
     "hn_conv_sc_supported": [POINTER(HnConv)],
     "hn_conv_sc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
+    "hn_conv_wgrad_sc_supported": [POINTER(HnConv)],
+    "hn_conv_wgrad_sc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _P],
     "hn_conv_wgrad_tc_supported": [POINTER(HnConv)],
     "hn_conv_wgrad_tc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _P],
     "hn_adamw_step": [_FP, _FP, _FP, _FP, _L, _F, _F, _F, _F, _F, _I, _F, _P],

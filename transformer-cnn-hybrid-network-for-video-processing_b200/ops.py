@@ -260,7 +260,12 @@ def _wgrad_raw(x1, x2, dz, dw, *, Creal, OH, OW, Cout, KH, KW, stride, pad, dil,
     d = _desc(B=B, H=H, W=W, C1=x1.shape[3], C2=C2, ld1=ld1, ld2=ld2, OH=OH, OW=OW, Cout=Cout, ldy=lddz, KH=KH,
               KW=KW, stride=stride, pad=pad, dil=dil, mode=0, ups=ups, act=0, pshuf=0, ldr=0,
               Kpad=lib.hn_conv_kpad(KH, KW, x1.shape[3] + C2))
-    name = "hn_conv_wgrad_tc" if (USE_TC and lib.hn_conv_wgrad_tc_supported(d)) else "hn_conv2d_wgrad"
+    if USE_SC and lib.hn_conv_wgrad_sc_supported(d):
+        name = "hn_conv_wgrad_sc"
+    elif USE_TC and lib.hn_conv_wgrad_tc_supported(d):
+        name = "hn_conv_wgrad_tc"
+    else:
+        name = "hn_conv2d_wgrad"
     call(name, d, x1.data_ptr(), _ptr(x2), dz.data_ptr(), dw.data_ptr(), Creal, *strides, _stream())
 
 
