@@ -32,6 +32,7 @@ WORKLOADS = {
     "latent2mask": ("latent2mask", 16, "dice", "latent-to-mask: frozen Encoder_32K -> Decoder_32K('mask') training (BASELINE configs[3] i)"),
 }
 DEFAULT_WORKLOAD = "ae32k_image"
+MUFU_TEXP_S = 4.647        # ex2.approx results/s (x1e12), scripts/mufu_bench.cu on B200 @ 1965 MHz
 
 
 def load_peaks():
@@ -115,7 +116,8 @@ def _attn_work(args, bwd):
     else:
         B, N, heads, D = args[5], args[6], args[7], args[8]
     f = 4.0 * B * heads * N * N * D
-    return (2.5 * f if bwd else f), 2.0 * B * N * heads * D * (8 if bwd else 4)
+    exps = float(B) * heads * N * N * (2 if bwd else 1)     # softmax exponentials (bwd recomputes P in dQ and in dK/dV)
+    return (2.5 * f if bwd else f), 2.0 * B * N * heads * D * (8 if bwd else 4), exps
 
 
 WORK = {
@@ -138,7 +140,8 @@ class KernelProfiler:
     @contextlib.contextmanager
     def __call__(self, name, args):
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        fl, by = WORK[name](args) if name in WORK else (0.0, 0.0)
+        w = WORK[name](args) if name in WORK else (0.0, 0.0)
+        fl, by, ex = w[0], w[1], (w[2] if len(w) > 2 else 0.0)
         if self.detail and name.startswith("hn_conv"):
             d = args[0]
             name = (f"{name}[{d.B}x{d.H}x{d.W} C{d.C1}+{d.C2}->{4 * d.pshuf if d.pshuf else d.Cout} k{d.KH} s{d.stride} "
@@ -146,13 +149,14 @@ class KernelProfiler:
         s.record()
         yield
         e.record()
-        self.events.append((name, s, e, fl, by))
+        self.events.append((name, s, e, fl, by, ex))
 
     def table(self):
         torch.cuda.synchronize()
         agg = {}
-        for name, s, e, fl, by in self.events:
-            a = agg.setdefault(name, {"ms": 0.0, "n": 0, "flops": 0.0, "bytes": 0.0})
+        for name, s, e, fl, by, ex in self.events:
+            a = agg.setdefault(name, {"ms": 0.0, "n": 0, "flops": 0.0, "bytes": 0.0, "exps": 0.0})
+            a["exps"] += ex
             a["ms"] += s.elapsed_time(e)
             a["n"] += 1
             a["flops"] += fl
@@ -175,6 +179,11 @@ def roofline_from(agg, steps, peaks):
               "launches_per_step": a["n"] // steps, "avg_launch_us": round(a["ms"] * 1e3 / a["n"], 1),
               "share_of_step": round(a["ms"] / total, 3),
               "algorithmic_per_launch": {"GFLOP": round(a["flops"] / a["n"] / 1e9, 3), "MB": round(a["bytes"] / a["n"] / 1e6, 2)}})
+    if a.get("exps", 0) > 0:
+        # attention with head dims 4..16 is bound by the softmax exponentials (MUFU ex2, 16 results/clk/SM =
+        # 4.647e12/s measured on this pool's B200 with scripts/mufu_bench.cu), not by the tensor pipe
+        r["xu"] = {"bound": "mufu_ex2", "achieved": round(a["exps"] / sec / 1e12, 3), "peak": MUFU_TEXP_S, "unit": "Texp/s",
+                   "frac": round(a["exps"] / sec / 1e12 / MUFU_TEXP_S, 4)}
     top = sorted(agg.items(), key=lambda kv: -kv[1]["ms"])[:6]
     r["top_kernels"] = {k: {"share": round(v["ms"] / total, 3), "TFLOP/s": round(v["flops"] / (v["ms"] / 1e3) / 1e12, 1) if v["ms"] else 0,
                             "GB/s": round(v["bytes"] / (v["ms"] / 1e3) / 1e9, 0) if v["ms"] else 0} for k, v in top}

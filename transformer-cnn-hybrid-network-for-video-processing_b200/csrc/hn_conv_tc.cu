@@ -9,7 +9,7 @@
 //   filter tap; out-of-image coordinates are zero-filled by TMA = the conv padding.
 //   128B-swizzled, it is exactly the canonical K-major SW128 UMMA operand.
 // * B tile: 2-D TMA box {64, BN} of the packed weights [N][K].
-// * warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-5 = epilogue
+// * warp 0 = TMA producer, warp 1 = MMA issuer (one thread), warps 2-9 = epilogue
 //   (tcgen05.ld -> bias/act/BN-statistics -> bf16 -> 16B global stores).
 // * persistent CTAs (<= 148), 2 TMEM accumulator stages so the epilogue of tile i
 //   overlaps the MMAs of tile i+1; 4-8 smem stages.
@@ -22,7 +22,7 @@ namespace {
 constexpr int BM = 128;
 // BKC = channels per K step: 64 (128-byte rows, SWIZZLE_128B) or 32 (64-byte rows, SWIZZLE_64B; the
 // C = 32 layers of UNet level 1)
-constexpr int NTHREADS_TC = 192;
+constexpr int NTHREADS_TC = 320;             // producer warp, MMA warp, 8 epilogue warps (2 per TMEM lane quadrant)
 constexpr int STAT_MAX = 2048;               // channels whose BN statistics one CTA can hold
 
 struct TcParams {
@@ -158,7 +158,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -241,7 +241,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + acc * ACC_STRIDE;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      // the two warps of a lane quadrant take alternate 32-column chunks
+      for (int c = (warp - 2) >> 2; c < BN / 32; c += 2) {
         uint32_t r[32];
         tmem_ld32(t_row + c * 32, r);
         const int n = nt * BN + c * 32;        // first GEMM column of this chunk
@@ -293,9 +294,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
     }
     if (p.ssum) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");            // the four epilogue warps only
+      asm volatile("bar.sync 1, 256;" ::: "memory");            // the eight epilogue warps only
       const int nstat = p.pshuf ? p.pshuf : p.Ntot;
-      for (int i = threadIdx.x - 64; i < nstat; i += 128) {
+      for (int i = threadIdx.x - 64; i < nstat; i += 256) {
         const float a = s_stat[0][i], b = s_stat[1][i];
         if (a != 0.f || b != 0.f) { atomicAdd(p.ssum + i, a); atomicAdd(p.ssq + i, b); }
       }
