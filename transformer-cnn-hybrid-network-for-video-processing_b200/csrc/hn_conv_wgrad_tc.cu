@@ -11,6 +11,7 @@
 // dimension and the partial results are reduced with fp32 atomics straight into the parameter
 // gradient at its own (OIHW) strides.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "hn_common.cuh"
 
@@ -208,10 +209,19 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
             if (n < p.Cout) {
               const int cg = (from2 ? p.C1 : 0) + c_off + c * 32;
               float* dst = p.dw + n * p.s_n + kh * p.s_kh + kw * p.s_kw;
+              if (p.s_c == 1 && cg + 32 <= p.Creal && ((reinterpret_cast<uintptr_t>(dst + cg) & 15) == 0)) {
+                // 1x1 weights: input channels are contiguous -> four fp32 adds per reduction op
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const float v = __uint_as_float(r[j]);
-                if (cg + j < p.Creal && v != 0.f) atomicAdd(dst + (cg + j) * p.s_c, v);
+                for (int j = 0; j < 32; j += 4)
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + cg + j), "f"(__uint_as_float(r[j])),
+                               "f"(__uint_as_float(r[j + 1])), "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                               : "memory");
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const float v = __uint_as_float(r[j]);
+                  if (cg + j < p.Creal && v != 0.f) atomicAdd(dst + (cg + j) * p.s_c, v);
+                }
               }
             }
           }
@@ -315,9 +325,11 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
   p.tgroups = (taps + tpj - 1) / tpj;
   p.tpj = (taps + p.tgroups - 1) / p.tgroups;
   const int jobs = p.mblocks * (p.ct1 + p.ct2) * p.tgroups;
-  // whole waves of 148 CTAs (one CTA per SM: 512 TMEM columns): the largest split count that keeps
-  // jobs * splits <= 2 * 148, at least 8 pixel tiles (512 px) per work item
-  int splits = (148 * 2) / jobs;
+  // one wave of 148 CTAs (one CTA per SM: 512 TMEM columns; measured: a second wave only doubles the
+  // flush atomics): the largest split count that keeps jobs * splits <= 148, >= 8 pixel tiles per item
+  static int waves = 0;
+  if (waves == 0) { const char* e = getenv("HN_WG_WAVES"); waves = e ? atoi(e) : 1; if (waves < 1) waves = 1; }
+  int splits = (148 * waves) / jobs;
   int max_splits = p.ptiles / 8 > 0 ? p.ptiles / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;

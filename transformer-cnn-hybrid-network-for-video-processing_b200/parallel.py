@@ -18,14 +18,16 @@ class GradArena:
                        if p.requires_grad and (used is None or n in used)]
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.group = process_group
-        n = sum(p.numel() for p in self.params)
+        # every gradient starts on a 16-byte boundary (vector reductions in the wgrad kernels); the few
+        # padding floats stay zero and ride along in the all-reduce
+        n = sum((p.numel() + 3) // 4 * 4 for p in self.params)
         dev = self.params[0].device
         self.arena = torch.zeros(n, dtype=torch.float32, device=dev)
         off = 0
         self.slices = []
         for p in self.params:
             self.slices.append((off, off + p.numel()))
-            off += p.numel()
+            off += (p.numel() + 3) // 4 * 4
         # buckets over the REVERSED parameter list (backward order), equal element counts
         order = list(range(len(self.params)))[::-1]
         per = max(1, n // max(1, buckets))
