@@ -61,7 +61,7 @@ class ClockSampler:
                     self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.05)
 
     def __enter__(self):
         self.t.start()
@@ -120,7 +120,17 @@ def _attn_work(args, bwd):
     return (2.5 * f if bwd else f), 2.0 * B * N * heads * D * (8 if bwd else 4), exps
 
 
+def _bn_work(P, C, passes):
+    return 0.0, 2.0 * P * C * passes
+
+
 WORK = {
+    # BatchNorm passes (bf16 tensors of P x C): arguments as in include/hybridnet.h
+    "hn_bn_apply": lambda a: _bn_work(a[7], a[8], 3 if a[1] else 2),
+    "hn_bn_relu_bwd_reduce": lambda a: _bn_work(a[6], a[7], 2),
+    "hn_bn_relu_bwd_apply": lambda a: _bn_work(a[9], a[10], 3),
+    "hn_bn_bwd_reduce": lambda a: _bn_work(a[6], a[7], 4 if a[3] else 3),
+    "hn_bn_bwd_apply": lambda a: _bn_work(a[8], a[9], 3),
     "hn_conv2d_fwd": lambda a: _conv_work(a),
     "hn_conv_tc_fwd": lambda a: _conv_work(a),
     "hn_conv_sc_fwd": lambda a: _conv_work(a),
@@ -165,6 +175,13 @@ class KernelProfiler:
 
 
 def roofline_from(agg, steps, peaks):
+    if any("[" in k for k in agg):            # --kernel-detail rows: the roofline object is per kernel, not per geometry
+        merged = {}
+        for k, v in agg.items():
+            m = merged.setdefault(k.split("[")[0], {"ms": 0.0, "n": 0, "flops": 0.0, "bytes": 0.0, "exps": 0.0})
+            for f in m:
+                m[f] += v.get(f, 0.0)
+        agg = merged
     total = sum(a["ms"] for a in agg.values())
     name, a = max(agg.items(), key=lambda kv: kv[1]["ms"])
     sec = a["ms"] / 1e3
@@ -222,7 +239,7 @@ def cpu_reference(workload, frames, steps, warmup):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
