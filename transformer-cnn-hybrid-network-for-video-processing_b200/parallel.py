@@ -17,6 +17,7 @@ class GradArena:
         self.params = [p for n, p in model.named_parameters()
                        if p.requires_grad and (used is None or n in used)]
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.exchange = True      # set False for rank-local passes (profiling): no collective is issued
         self.group = process_group
         # every gradient starts on a 16-byte boundary (vector reductions in the wgrad kernels); the few
         # padding floats stay zero and ride along in the all-reduce
@@ -69,6 +70,8 @@ class GradArena:
 
     def _make_hook(self, i):
         def hook(_p):
+            if not self.exchange:
+                return
             b = self.bucket_of[i]
             self.pending[b] -= 1
             if self.pending[b] == 0:
@@ -87,7 +90,7 @@ class GradArena:
 
     def finish(self):
         """Join the exchange; gradients become the mean over ranks."""
-        if self.world == 1:
+        if self.world == 1 or not self.exchange:
             return
         for b, left in enumerate(self.pending):       # buckets whose params got no grad this step
             if left > 0:
