@@ -281,6 +281,7 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         import datetime
+        os.environ["NCCL_DEBUG"] = os.environ.get("HN_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     _lib.call("hn_check_device")
     torch.manual_seed(0)

@@ -191,6 +191,10 @@ int hn_attn_bwd(const void* q, const void* k, const void* v, const void* o, cons
  * through pshuf.  A: 4-D TMA boxes shifted per tap (OOB zero fill = padding), B: packed weights,
  * accumulators in TMEM, persistent CTAs.  hn_conv_tc_supported() tells the host which path to use. */
 int hn_conv_tc_supported(const HnConv* d);
+/* 1 when hn_conv_tc_fwd takes its halo variant for d (3x3 stride 1, W % 128 == 0, weights resident in smem:
+ * one TMA box of 128+2*pad pixels per filter row instead of one per tap) -- the host prefers it over
+ * hn_conv_sc_fwd for the C = 32 / 64 layers. */
+int hn_conv_tc_halo_supported(const HnConv* d);
 int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
                       const float* bias, void* y, float* stat_sum, float* stat_sqsum,
                       void* stream);

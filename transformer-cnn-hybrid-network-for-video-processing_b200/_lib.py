@@ -64,6 +64,7 @@ SIGNATURES = {
     "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _P, _P, _P, _I, _I, _I, _I,
                     _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_conv_tc_supported": [POINTER(HnConv)],
+    "hn_conv_tc_halo_supported": [POINTER(HnConv)],
     "hn_conv_tc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
     "hn_conv_sc_supported": [POINTER(HnConv)],
     "hn_conv_sc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],

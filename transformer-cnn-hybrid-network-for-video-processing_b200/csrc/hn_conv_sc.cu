@@ -119,6 +119,50 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
 #pragma unroll
         for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = acc[i][j][2] = acc[i][j][3] = 0.f;
 
+      if (CG >= 2) {
+        // K order (tap, c8) with an even chunk count per tap: tap outer, so the halo address of a pixel
+        // is computed once per (tap, m-tile) and a k-step only XORs the chunk index into it
+        const int kpt = CG >> 1;                              // k16 steps per tap
+        const int taps = p.KH * p.KW;
+        int ks = 0;
+        for (int tap = 0; tap < taps; ++tap) {
+          const int tp = s_tap[tap];
+          const int dr = tp >> 16, dc = tp & 0xFFFF;
+          uint32_t abase[MT];
+          int akey[MT];
+#pragma unroll
+          for (int i = 0; i < MT; ++i) {
+            const int mt = pass * MT + i;
+            const int r = warp * 2 + (mt >> 1) + dr;
+            const int c = (mt & 1) * 16 + (lane & 15) + dc;
+            abase[i] = smem_u32(sHc) + (uint32_t)(((r * p.WR + c) << p.lgCG) * 16);
+            akey[i] = (c >> p.sh) & cgm;
+          }
+          for (int kk = 0; kk < kpt; ++kk, ++ks) {
+            uint32_t bfr[NT][2];
+            if (NT >= 2) {
+#pragma unroll
+              for (int j = 0; j < NT; j += 2) {
+                const int row = j * 8 + (lane & 7) + ((lane >> 4) << 3);
+                const int ch = ks * 2 + ((lane >> 3) & 1);
+                ldsm_x4(bfr[j][0], bfr[j][1], bfr[j + 1 < NT ? j + 1 : j][0], bfr[j + 1 < NT ? j + 1 : j][1],
+                        smem_u32(sW + row * p.wrow + ch * 16));
+              }
+            } else {
+              ldsm_x2(bfr[0][0], bfr[0][1], smem_u32(sW + (lane & 7) * p.wrow + (ks * 2 + ((lane >> 3) & 1)) * 16));
+            }
+            const int c8 = kk * 2 + (lane >> 4);
+            uint32_t af[MT][4];                               // all A fragments first: the MMAs then issue back to back
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+              ldsm_x4(af[i][0], af[i][1], af[i][2], af[i][3], abase[i] + (uint32_t)((c8 ^ akey[i]) << 4));
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+#pragma unroll
+              for (int j = 0; j < NT; ++j) mma_16816(acc[i][j], af[i], bfr[j][0], bfr[j][1]);
+          }
+        }
+      } else
       for (int ks = 0; ks < p.KS; ++ks) {
         // B fragments (weights) for this k-step
         uint32_t bfr[NT][2];

@@ -14,6 +14,7 @@
 // * persistent CTAs (<= 148), 2 TMEM accumulator stages so the epilogue of tile i
 //   overlaps the MMAs of tile i+1; 4-8 smem stages.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "hn_common.cuh"
 
@@ -23,7 +24,8 @@ constexpr int BM = 128;
 // BKC = channels per K step: 64 (128-byte rows, SWIZZLE_128B) or 32 (64-byte rows, SWIZZLE_64B; the
 // C = 32 layers of UNet level 1)
 constexpr int NTHREADS_TC = 320;             // producer warp, MMA warp, 8 epilogue warps (2 per TMEM lane quadrant)
-constexpr int STAT_MAX = 2048;               // channels whose BN statistics one CTA can hold
+constexpr int STAT_MAX = 2048;
+constexpr int HALO_STAT_MAX = 256;          // the halo variant keeps BN = N <= 256               // channels whose BN statistics one CTA can hold
 
 struct TcParams {
   int B, H, W;
@@ -310,6 +312,184 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   }
 }
 
+// ---- halo variant: 3x3 stride-1 convs on maps with W % 128 == 0 and resident weights ------------------
+// A tile is 128 consecutive pixels of ONE image row.  Per (kh, 64/32-channel chunk) the producer fetches a
+// single box of 128 + 2*pad pixels; the three kw taps are the same box read through descriptors whose start
+// address is advanced by kw*dil rows -- every activation byte crosses L2 -> SM three times instead of nine.
+// All packed weights of the layer ((taps, Cin) x BN) stay resident in shared memory for the CTA's lifetime.
+constexpr int HALO_MAX_WBYTES = 110 * 1024;
+template <int ROWB>
+__device__ __forceinline__ uint64_t make_kmajor_desc_rows(uint32_t smem_addr, int use_base_offset) {
+  uint64_t d = make_kmajor_desc<ROWB>(smem_addr);
+  // Measured on B200 (scripts/check_halo.py): the 128B/64B swizzle XOR is taken from the ABSOLUTE shared-memory
+  // address bits, exactly as TMA wrote the box, so a start address advanced by whole rows needs base_offset = 0;
+  // setting base_offset = (addr >> 7) & 7 gives wrong operands.  The switch stays for experiments.
+  if (use_base_offset) d |= (uint64_t)((smem_addr >> 7) & 7) << 49;
+  return d;
+}
+
+template <int BN, int BKC>
+__global__ void __launch_bounds__(NTHREADS_TC, 1)
+conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
+                    const __grid_constant__ CUtensorMap mapB, const TcParams p, const int stage_bytes, const int stages,
+                    const int halo_tx_bytes, const int base_off_mode) {
+  constexpr int ROWB = BKC * 2;
+  constexpr int B_BYTES = BN * BKC * 2;
+  constexpr int ACC_STRIDE = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
+  constexpr int TMEM_COLS = 2 * ACC_STRIDE;
+  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t bars[2 * 8 + 5];
+  __shared__ uint32_t tmem_base_slot;
+  __shared__ float s_stat[2][HALO_STAT_MAX];
+  if (p.ssum) {
+    for (int i = threadIdx.x; i < 2 * HALO_STAT_MAX; i += NTHREADS_TC) (&s_stat[0][0])[i] = 0.f;
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[8]);
+  const uint32_t tfull0 = smem_u32(&bars[16]), tempty0 = smem_u32(&bars[18]), wfull = smem_u32(&bars[20]);
+  const int taps = p.KH * p.KW;
+  const int kit_tap = p.kiters_per_tap1 + p.kiters_per_tap2;
+  const int wboxes = taps * kit_tap;                         // resident weight boxes of B_BYTES each
+  uint8_t* sWt = smem;
+  uint8_t* sA = smem + ((wboxes * B_BYTES + 1023) & ~1023);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 8); }
+    mbar_init(wfull, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+  const int total_tiles = p.m_tiles;                         // n_tiles == 1 by construction
+  const int row_steps = p.KH * kit_tap;                      // stages consumed per tile
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA1) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+      mbar_arrive_expect_tx(wfull, wboxes * B_BYTES);
+      for (int i = 0; i < wboxes; ++i) tma_load_2d(smem_u32(sWt + i * B_BYTES), &mapB, wfull, i * BKC, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int tw = tile % p.tiles_w, h = (tile / p.tiles_w) % p.H, b = tile / (p.tiles_w * p.H);
+        const int w0 = tw * 128;
+        for (int kh = 0; kh < p.KH; ++kh) {
+          const int hh = h + kh * p.dil - p.pad;
+          for (int kc = 0; kc < kit_tap; ++kc) {
+            mbar_wait(empty0 + 8 * stage, phase ^ 1);
+            const uint32_t sa = smem_u32(sA + stage * stage_bytes);
+            mbar_arrive_expect_tx(full0 + 8 * stage, halo_tx_bytes);
+            if (kc < p.kiters_per_tap1) tma_load_4d(sa, &mapA1, full0 + 8 * stage, kc * BKC, w0 - p.pad, hh, b);
+            else tma_load_4d(sa, &mapA2, full0 + 8 * stage, (kc - p.kiters_per_tap1) * BKC, w0 - p.pad, hh, b);
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      mbar_wait(wfull, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const int acc = lt & 1;
+        const uint32_t acc_phase = (lt >> 1) & 1;
+        mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
+        int rs = 0;
+        for (int kh = 0; kh < p.KH; ++kh) {
+          for (int kc = 0; kc < kit_tap; ++kc, ++rs) {
+            mbar_wait(full0 + 8 * stage, phase);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(sA + stage * stage_bytes);
+            for (int kw = 0; kw < p.KW; ++kw) {
+              const uint64_t da = make_kmajor_desc_rows<ROWB>(sa + kw * p.dil * ROWB, base_off_mode);
+              const uint64_t db = make_kmajor_desc<ROWB>(smem_u32(sWt + ((kh * p.KW + kw) * kit_tap + kc) * B_BYTES));
+#pragma unroll
+              for (int k = 0; k < BKC / 16; ++k)
+                umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (rs > 0 || kw > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(empty0 + 8 * stage);
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+          }
+        }
+        umma_commit(tfull0 + 8 * acc);
+      }
+    }
+  } else {
+    const int lane_base = (warp & 3) * 32;
+    const int row = lane_base + lane;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int tw = tile % p.tiles_w, h = (tile / p.tiles_w) % p.H, b = tile / (p.tiles_w * p.H);
+      const int w = tw * 128 + row;
+      const int acc = lt & 1;
+      const uint32_t acc_phase = (lt >> 1) & 1;
+      mbar_wait(tfull0 + 8 * acc, acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + acc * ACC_STRIDE;
+      const long long pix = ((long long)b * p.H + h) * p.W + w;
+#pragma unroll 1
+      for (int c = (warp - 2) >> 2; c < BN / 32; c += 2) {
+        uint32_t r[32];
+        tmem_ld32(t_row + c * 32, r);
+        const int ch0 = c * 32;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(p.bias + ch0 + j) : 0.f);
+        if (p.ssum) {
+          float t[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) t[j] = bf16_round(v[j]);
+          float s = colsum32(t, lane);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { float q = bf16_round(v[j]); t[j] = q * q; }
+          float q = colsum32(t, lane);
+          atomicAdd(&s_stat[0][ch0 + lane], s);
+          atomicAdd(&s_stat[1][ch0 + lane], q);
+        }
+        bf16* dst = p.y + pix * p.ldy + ch0;
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          float o[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[e] = apply_act(v[j + e], p.act);
+          store8(dst + j, o);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+    }
+    if (p.ssum) {
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      for (int i = threadIdx.x - 64; i < BN; i += 256) {
+        const float a = s_stat[0][i], bq = s_stat[1][i];
+        if (a != 0.f || bq != 0.f) { atomicAdd(p.ssum + i, a); atomicAdd(p.ssq + i, bq); }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
 // ---- host side -------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -405,7 +585,66 @@ int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b
   return HN_OK;
 }
 
+// ---- halo variant host side ------------------------------------------------------------------------
+int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+bool halo_ok(const HnConv* d) {
+  static int enabled = -1;
+  if (enabled < 0) enabled = env_int("HN_TC_HALO", 1);
+  if (!enabled || !tc_ok(d)) return false;
+  if (d->stride != 1 || d->pshuf || d->KH != 3 || d->KW != 3 || d->pad != d->dil || d->dil > 4) return false;
+  if (d->W % 128) return false;
+  const int bkc = pick_bkc(d);
+  const int n = d->Cout;
+  if (bkc == 32 ? (n != 32 && n != 64) : (n != 64 && n != 128)) return false;
+  const int wbytes = 9 * (d->C1 + d->C2) * n * 2;
+  return wbytes <= HALO_MAX_WBYTES;
+}
+template <int BN, int BKC>
+int launch_halo(const HnConv* d, const void* x1, const void* x2, const void* wpacked, TcParams p, cudaStream_t st) {
+  const int rows = 128 + 2 * d->pad;
+  const int halo_tx = rows * BKC * 2;
+  const int stage_bytes = (halo_tx + 1023) & ~1023;
+  const int wbytes = ((9 * (d->C1 + d->C2) * BN * 2) + 1023) & ~1023;
+  int stages = (200 * 1024 - wbytes) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 2) HN_FAIL(HN_EUNSUPPORTED, "conv_tc_halo: weights leave no room for the pipeline");
+  const int SMEM = wbytes + stages * stage_bytes + 1024;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_halo_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024 + 1024);
+    if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "conv_tc_halo: smem attribute: %s", cudaGetErrorString(e));
+    configured = true;
+  }
+  static int base_off = -1;
+  if (base_off < 0) base_off = env_int("HN_TC_BASEOFF", 0);
+  // A boxes: {BKC channels, 128 + 2*pad pixels of one row}
+  CUtensorMap a1, a2, bm;
+  TileGeom g; g.BW = rows; g.BH = 1; g.BB = 1;
+  int rc = make_map_act(&a1, x1, d->B, d->H, d->W, d->C1, d->ld1, g, 1, BKC);
+  if (rc) HN_FAIL(HN_ECUDA, "conv_tc_halo: cuTensorMapEncodeTiled(A1) = %d", rc);
+  if (d->C2) {
+    rc = make_map_act(&a2, x2, d->B, d->H, d->W, d->C2, d->ld2, g, 1, BKC);
+    if (rc) HN_FAIL(HN_ECUDA, "conv_tc_halo: cuTensorMapEncodeTiled(A2) = %d", rc);
+  } else {
+    a2 = a1;
+  }
+  rc = make_map_w(&bm, wpacked, hn_conv_npad(BN), d->Kpad, BN, BKC);
+  if (rc) HN_FAIL(HN_ECUDA, "conv_tc_halo: cuTensorMapEncodeTiled(B) = %d", rc);
+  p.tiles_w = d->W / 128; p.tiles_h = d->H; p.BW = 128; p.BH = 1; p.BB = 1;
+  p.m_tiles = (int)((long long)d->B * d->H * d->W / 128); p.n_tiles = 1;
+  p.kiters_per_tap1 = d->C1 / BKC; p.kiters_per_tap2 = d->C2 / BKC;
+  const int grid = p.m_tiles < 148 ? p.m_tiles : 148;
+  conv_tc_halo_kernel<BN, BKC><<<grid, NTHREADS_TC, SMEM, st>>>(a1, a2, bm, p, stage_bytes, stages, halo_tx, base_off);
+  HN_CHECK_LAUNCH("conv_tc_halo_kernel");
+  return HN_OK;
+}
+
 }  // namespace
+
+extern "C" int hn_conv_tc_halo_supported(const HnConv* d) { return halo_ok(d) ? 1 : 0; }
 
 extern "C" int hn_conv_tc_supported(const HnConv* d) { return tc_ok(d) ? 1 : 0; }
 
@@ -416,6 +655,16 @@ extern "C" int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, c
   HN_REQUIRE((stat_sum == nullptr) == (stat_sqsum == nullptr), "conv_tc_fwd: stats need both buffers");
   HN_REQUIRE(stat_sum == nullptr || (d->pshuf ? d->pshuf : d->Cout) <= STAT_MAX, "conv_tc_fwd: too many channels for fused statistics");
   HN_REQUIRE(((uintptr_t)x1 % 16) == 0 && ((uintptr_t)wpacked % 16) == 0 && ((uintptr_t)y % 16) == 0, "conv_tc_fwd: 16B alignment");
+  if (halo_ok(d)) {
+    TcParams hp;
+    hp.B = d->B; hp.H = d->OH; hp.W = d->OW; hp.C1 = d->C1; hp.C2 = d->C2; hp.Cout = d->Cout; hp.Ntot = d->Cout; hp.ldy = d->ldy;
+    hp.KH = d->KH; hp.KW = d->KW; hp.pad = d->pad; hp.dil = d->dil; hp.es = 1;
+    hp.act = d->act; hp.pshuf = 0; hp.bias = bias; hp.y = (bf16*)y; hp.ssum = stat_sum; hp.ssq = stat_sqsum;
+    HN_REQUIRE(d->Kpad == d->KH * d->KW * (d->C1 + d->C2), "conv_tc_fwd: Kpad mismatch");
+    cudaStream_t hst = (cudaStream_t)stream;
+    if (pick_bkc(d) == 32) return d->Cout == 32 ? launch_halo<32, 32>(d, x1, x2, wpacked, hp, hst) : launch_halo<64, 32>(d, x1, x2, wpacked, hp, hst);
+    return d->Cout == 64 ? launch_halo<64, 64>(d, x1, x2, wpacked, hp, hst) : launch_halo<128, 64>(d, x1, x2, wpacked, hp, hst);
+  }
   TileGeom g;
   tile_geom(d->B, d->OH, d->OW, &g);
   const int ntot = d->pshuf ? 4 * d->pshuf : d->Cout;
