@@ -79,6 +79,21 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// one lane of a fully converged warp (CUTLASS elect_one_sync): the MMA warp runs its loops warp-uniformly and
+// only the tcgen05 instructions sit under this predicate, so descriptors stay in uniform registers (issuing from
+// inside an `if (lane == 0)` region made ptxas wrap every UTCHMMA in a vote/elect loop: ~330 SASS instructions
+// per pipeline stage, which bound every small-stage layer)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, P;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
@@ -203,29 +218,33 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        const int acc = lt & 1;
-        const uint32_t acc_phase = (lt >> 1) & 1;
-        mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+    const bool leader = elect_one();
+    const uint32_t smem_base = smem_u32(smem);
+    int stage = 0;
+    uint32_t phase = 0;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int acc = lt & 1;
+      const uint32_t acc_phase = (lt >> 1) & 1;
+      mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
+      for (int kit = 0; kit < kiters; ++kit) {
+        mbar_wait(full0 + 8 * stage, phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
-        for (int kit = 0; kit < kiters; ++kit) {
-          mbar_wait(full0 + 8 * stage, phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
-          const uint64_t da = make_kmajor_desc<BKC * 2>(sa), db = make_kmajor_desc<BKC * 2>(sa + A_BYTES);
+        const uint32_t sa = smem_base + stage * STAGE_BYTES;
+        const uint64_t da = make_kmajor_desc<BKC * 2>(sa), db = make_kmajor_desc<BKC * 2>(sa + A_BYTES);
+        if (leader) {
 #pragma unroll
           for (int k = 0; k < BKC / 16; ++k)
             umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (kit > 0 || k > 0) ? 1u : 0u);
           umma_commit(empty0 + 8 * stage);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tfull0 + 8 * acc);
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      if (leader) umma_commit(tfull0 + 8 * acc);
+      __syncwarp();
     }
   } else {
     // ---- epilogue warps: TMEM lanes [32*(warp%4), +32) = tile rows ----------------------
@@ -358,7 +377,9 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 8); }
+    // BN == 32 has a single 32-column chunk: the two epilogue teams (4 warps each) then take alternate TILES
+    // (team t owns TMEM accumulator t); wider tiles are split by column chunks between the teams
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, BN == 32 ? 4 : 8); }
     mbar_init(wfull, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -398,36 +419,41 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      mbar_wait(wfull, 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      int lt = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        const int acc = lt & 1;
-        const uint32_t acc_phase = (lt >> 1) & 1;
-        mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
-        int rs = 0;
-        for (int kh = 0; kh < p.KH; ++kh) {
-          for (int kc = 0; kc < kit_tap; ++kc, ++rs) {
-            mbar_wait(full0 + 8 * stage, phase);
-            tc_fence_after();
-            const uint32_t sa = smem_u32(sA + stage * stage_bytes);
-            for (int kw = 0; kw < p.KW; ++kw) {
+    const bool leader = elect_one();
+    const uint32_t sA_base = smem_u32(sA), sW_base = smem_u32(sWt);
+    mbar_wait(wfull, 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int acc = lt & 1;
+      const uint32_t acc_phase = (lt >> 1) & 1;
+      mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
+      int rs = 0;
+      for (int kh = 0; kh < p.KH; ++kh) {
+        for (int kc = 0; kc < kit_tap; ++kc, ++rs) {
+          mbar_wait(full0 + 8 * stage, phase);
+          tc_fence_after();
+          const uint32_t sa = sA_base + stage * stage_bytes;
+          if (leader) {
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
               const uint64_t da = make_kmajor_desc_rows<ROWB>(sa + kw * p.dil * ROWB, base_off_mode);
-              const uint64_t db = make_kmajor_desc<ROWB>(smem_u32(sWt + ((kh * p.KW + kw) * kit_tap + kc) * B_BYTES));
+              const uint64_t db = make_kmajor_desc<ROWB>(sW_base + ((kh * 3 + kw) * kit_tap + kc) * B_BYTES);
 #pragma unroll
               for (int k = 0; k < BKC / 16; ++k)
                 umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (rs > 0 || kw > 0 || k > 0) ? 1u : 0u);
             }
             umma_commit(empty0 + 8 * stage);
-            if (++stage == stages) { stage = 0; phase ^= 1; }
           }
+          __syncwarp();
+          if (++stage == stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tfull0 + 8 * acc);
       }
+      if (leader) umma_commit(tfull0 + 8 * acc);
+      __syncwarp();
     }
   } else {
     const int lane_base = (warp & 3) * 32;
@@ -438,12 +464,14 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
       const int w = tw * 128 + row;
       const int acc = lt & 1;
       const uint32_t acc_phase = (lt >> 1) & 1;
+      const int team = (warp - 2) >> 2;
+      if (BN == 32 && acc != team) continue;
       mbar_wait(tfull0 + 8 * acc, acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + acc * ACC_STRIDE;
       const long long pix = ((long long)b * p.H + h) * p.W + w;
 #pragma unroll 1
-      for (int c = (warp - 2) >> 2; c < BN / 32; c += 2) {
+      for (int c = (BN == 32 ? 0 : team); c < BN / 32; c += (BN == 32 ? 1 : 2)) {
         uint32_t r[32];
         tmem_ld32(t_row + c * 32, r);
         const int ch0 = c * 32;
