@@ -115,10 +115,14 @@ int hn_maxpool2_bwd(const void* x, const void* dy, void* dx, int B, int H, int W
 /* gradient of nearest Upsample(x2): dx[h,w] = sum of the 2x2 block of dy */
 int hn_upsample2_bwd(const void* dy, void* dx, int B, int H, int W, int C, int lddy, int lddx,
                      void* stream);
-/* Dropout / Dropout2d: y = x * keep/(1-p); keep bit = hash(seed, idx) (idx = element,
- * or (b,c) when channelwise).  The same call with dy gives the backward.        */
+/* Dropout / Dropout2d: y = x * keep/(1-p); keep bit = hash(seed', idx) (idx = element,
+ * or (b,c) when channelwise).  The same call with dy gives the backward.
+ * seed' = seed when step_counter is NULL, else seed + *step_counter * 0x9E3779B97F4A7C15:
+ * step_counter is a DEVICE u64 read by the kernel, so that a training step captured once in a
+ * CUDA graph still draws a fresh mask on every replay (the graph bumps the counter itself).   */
 int hn_dropout(const void* x, void* y, int B, long long HW, int C, int ldx, int ldy, float p,
-               unsigned long long seed, int channelwise, void* stream);
+               unsigned long long seed, const unsigned long long* step_counter, int channelwise,
+               void* stream);
 
 /* ---- LayerNorm over C (FCT.py:32-36,89) ------------------------------------- */
 int hn_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, long long P,

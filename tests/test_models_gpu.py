@@ -329,3 +329,79 @@ def test_ae32k_eval_mode_gradients(name):
     if name == "latent2mask":
         f_grads = {k: v for k, v in f_grads.items() if k.startswith("1.")}
     _compare(outs, f_outs, grads, f_grads, pcos=0.98)
+
+
+@pytest.mark.gpu
+def test_captured_step_matches_eager_and_redraws_dropout():
+    """parallel.CapturedStep: the CUDA-graph replay of a step gives the eager step's loss and gradients
+    (dropout off), and with dropout on every replay draws a new mask (device step counter)."""
+    import hybridnet
+    from hybridnet import ops, parallel
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    m = hybridnet.UNet().to(dev).train()
+    arena = parallel.GradArena(m)
+    x = torch.rand(2, 3, 64, 64, device=dev)
+    y = (torch.rand(2, 1, 64, 64, device=dev) > 0.5).float()
+
+    def step(xd, yd):
+        arena.zero_grad()
+        ops.invalidate_packed()
+        out = m(xd)
+        p, t = out[:, 0].reshape(-1), yd[:, 0].reshape(-1)
+        loss = 1.0 - (2.0 * torch.dot(p, t) + 1.0) / (p.sum() + t.sum() + 1.0)
+        loss.backward()
+        arena.finish()
+        return loss
+
+    # BN running statistics move every step; compare single steps from the same state
+    state = {k: v.clone() for k, v in m.state_dict().items()}
+    cap = parallel.CapturedStep(step, x, y, warmup=1)
+    assert cap.launches > 50
+
+    def run(fn, *a):
+        m.load_state_dict(state)
+        l = float(fn(*a))
+        return l, arena.arena.clone()
+
+    def rel(a, b):
+        return float((a - b).norm() / b.norm())
+
+    # train-mode BN: batch statistics are summed with fp32 atomics, so two EAGER runs already differ (a
+    # last-bit change of a statistic flips bf16 roundings downstream, amplified by 18 BN layers at 2x64x64);
+    # the replay must sit inside that same noise band
+    l_e1, g_e1 = run(step, x, y)
+    l_e2, g_e2 = run(step, x, y)
+    l_g, g_g = run(cap, x, y)
+    noise = max(rel(g_e1, g_e2), 1e-3)
+    assert abs(l_e1 - l_g) < max(1e-4, 3 * abs(l_e1 - l_e2))
+    assert rel(g_g, g_e1) < 3 * noise, (rel(g_g, g_e1), noise)
+    # a different batch (pinned host tensor) through the same graph
+    x2 = torch.rand(2, 3, 64, 64).pin_memory()
+    l2, _ = run(cap, x2, y)
+    l2_eager, _ = run(step, x2.to(dev), y)
+    assert abs(l2 - l2_eager) < max(1e-4, 3 * abs(l_e1 - l_e2)) and abs(l2 - l_g) > 2e-4
+
+    # eval-mode BN (running statistics, no atomics on the activation path): replay == eager up to the
+    # summation order of the weight-gradient flush
+    m.eval()
+    cap_eval = parallel.CapturedStep(step, x, y, warmup=1)
+    l_e, g_e = run(step, x, y)
+    l_c, g_c = run(cap_eval, x, y)
+    assert abs(l_e - l_c) < 1e-6
+    assert rel(g_c, g_e) < 1e-3
+
+    # dropout: FCT has Dropout(0.3)/(0.1) on the path; replays of one graph must not repeat the mask
+    f = hybridnet.FCT().to(dev).train()
+    fa = parallel.GradArena(f, used={n for n, p in f.named_parameters() if n not in parallel.used_parameter_names("fct")})
+
+    def fstep(xd, yd):
+        fa.zero_grad()
+        out = f(xd)
+        loss = out.mean()
+        loss.backward()
+        return loss
+
+    fc = parallel.CapturedStep(fstep, x, y, warmup=1)
+    losses = {round(float(fc()), 7) for _ in range(4)}
+    assert len(losses) == 4, losses

@@ -46,7 +46,7 @@ SIGNATURES = {
     "hn_maxpool2_fwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
     "hn_maxpool2_bwd": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P],
     "hn_upsample2_bwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
-    "hn_dropout": [_P, _P, _I, _L, _I, _I, _I, _F, c_ulonglong, _I, _P],
+    "hn_dropout": [_P, _P, _I, _L, _I, _I, _I, _F, c_ulonglong, _P, _I, _P],
     "hn_layernorm_fwd": [_P, _P, _FP, _FP, _L, _I, _I, _I, _F, _P],
     "hn_layernorm_bwd": [_P, _P, _P, _FP, _FP, _FP, _L, _I, _I, _I, _I, _F, _P],
     "hn_bn_stats": [_P, _L, _I, _I, _FP, _FP, _P],

@@ -284,7 +284,10 @@ __global__ void gelu3_bwd_kernel(const bf16* __restrict__ dy, const bf16* __rest
 // channelwise (Dropout2d): one hash per (b, c) plane index.
 __global__ void __launch_bounds__(256) dropout_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int B,
                                                       long long HW, int C, int ldx, int ldy, float p,
-                                                      unsigned long long seed, int channelwise) {
+                                                      unsigned long long seed,
+                                                      const unsigned long long* __restrict__ step_counter,
+                                                      int channelwise) {
+  if (step_counter) seed += __ldg(step_counter) * 0x9E3779B97F4A7C15ull;
   const int CV = C / 8;
   const long long P = (long long)B * HW;
   const float scale = 1.f / (1.f - p);
@@ -390,10 +393,10 @@ extern "C" int hn_gelu3_sum_bwd(const void* dy, const void* z1, const void* z2, 
   HN_CHECK_LAUNCH("gelu3_bwd");
   return HN_OK;
 }
-extern "C" int hn_dropout(const void* x, void* y, int B, long long HW, int C, int ldx, int ldy, float p, unsigned long long seed, int channelwise, void* stream) {
+extern "C" int hn_dropout(const void* x, void* y, int B, long long HW, int C, int ldx, int ldy, float p, unsigned long long seed, const unsigned long long* step_counter, int channelwise, void* stream) {
   REQ_CV(C, "dropout");
   HN_REQUIRE(x && y && p >= 0.f && p < 1.f, "dropout: bad args");
-  dropout_kernel<<<grid_for((long long)B * HW * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (bf16*)y, B, HW, C, ldx, ldy, p, seed, channelwise);
+  dropout_kernel<<<grid_for((long long)B * HW * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (bf16*)y, B, HW, C, ldx, ldy, p, seed, step_counter, channelwise);
   HN_CHECK_LAUNCH("dropout");
   return HN_OK;
 }

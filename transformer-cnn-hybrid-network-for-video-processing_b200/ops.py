@@ -591,11 +591,26 @@ def maxpool2(x):
 
 
 _dropout_seed = [0x5DEECE66D]
+_step_counter = {}        # device -> u64 tensor read by hn_dropout (see bump_step_counter)
 
 
 def manual_seed(seed):
     """Seed of the stateless dropout hash (per-rank under data parallelism)."""
     _dropout_seed[0] = int(seed) & ((1 << 62) - 1)
+
+
+def step_counter(device):
+    """Device-resident step counter mixed into every dropout seed by the kernel itself."""
+    t = _step_counter.get(device)
+    if t is None:
+        t = _step_counter[device] = torch.zeros(1, dtype=torch.int64, device=device)
+    return t
+
+
+def bump_step_counter(device):
+    """One in-place device add: inside a captured step it makes every graph replay draw new dropout
+    masks although the host-side seeds were frozen at capture time."""
+    step_counter(device).add_(1)
 
 
 class _DropoutFn(torch.autograd.Function):
@@ -604,8 +619,9 @@ class _DropoutFn(torch.autograd.Function):
         x, ld = nhwc(x)
         B, H, W, C = x.shape
         y = _new(B, H, W, C, x)
-        call("hn_dropout", x.data_ptr(), y.data_ptr(), B, H * W, C, ld, C, p, seed, int(channelwise), _stream())
-        ctx.p, ctx.cw, ctx.seed = p, channelwise, seed
+        ctr = step_counter(x.device)
+        call("hn_dropout", x.data_ptr(), y.data_ptr(), B, H * W, C, ld, C, p, seed, ctr.data_ptr(), int(channelwise), _stream())
+        ctx.p, ctx.cw, ctx.seed, ctx.ctr = p, channelwise, seed, ctr
         return y
 
     @staticmethod
@@ -613,7 +629,7 @@ class _DropoutFn(torch.autograd.Function):
         dy, ld = nhwc(dy)
         B, H, W, C = dy.shape
         dx = _new(B, H, W, C, dy)
-        call("hn_dropout", dy.data_ptr(), dx.data_ptr(), B, H * W, C, ld, C, ctx.p, ctx.seed, int(ctx.cw), _stream())
+        call("hn_dropout", dy.data_ptr(), dx.data_ptr(), B, H * W, C, ld, C, ctx.p, ctx.seed, ctx.ctr.data_ptr(), int(ctx.cw), _stream())
         return dx, None, None, None
 
 

@@ -103,6 +103,57 @@ class GradArena:
         self.arena.mul_(1.0 / self.world)
 
 
+class CapturedStep:
+    """One training step (zero-grad, weight repack, forward, loss, backward, gradient exchange) recorded
+    ONCE into a CUDA graph and replayed per batch: the ~700 kernel launches of a step leave the host as a
+    single ``cudaGraphLaunch`` instead of ~700 Python/ctypes dispatches, which is what bounds the eager
+    step once the kernels are fast (the reference's trainers issue every op eagerly,
+    ``FCT.py:326-338`` / ``Model.py:54-60``).
+
+    ``fn(x, y) -> loss`` must be capture-safe: device work only on the current stream (all hn_* entry
+    points are), no host synchronisation.  Inputs are copied into static device buffers (``x``/``y`` may be
+    pinned host tensors: the H2D copy is part of the call); the returned loss is a static device scalar.
+    Dropout masks still change per replay: the graph bumps the device step counter that ``hn_dropout``
+    mixes into its seed (``ops.bump_step_counter``)."""
+
+    def __init__(self, fn, x, y, warmup=3):
+        from . import _lib, ops
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.x = torch.empty(x.shape, dtype=x.dtype, device=dev)
+        self.y = torch.empty(y.shape, dtype=y.dtype, device=dev)
+        self.x.copy_(x)
+        self.y.copy_(y)
+
+        def body():
+            ops.bump_step_counter(dev)
+            return fn(self.x, self.y)
+
+        # AccumulateGrad nodes that outlive an earlier eager step remember that step's stream; autograd then
+        # orders the capture stream against it with events (harmless, checked by the eager-vs-replay test)
+        if hasattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch"):
+            torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.stats["launches"]
+        with torch.cuda.graph(self.graph):
+            self.loss = body()
+        self.launches = _lib.stats["launches"] - n0      # hn_* kernels recorded in the graph (per replay)
+
+    def __call__(self, x=None, y=None):
+        if x is not None:
+            self.x.copy_(x, non_blocking=True)
+        if y is not None:
+            self.y.copy_(y, non_blocking=True)
+        self.graph.replay()
+        return self.loss
+
+
 def used_parameter_names(model_name):
     """Parameters that ever receive a gradient (SURVEY note U: 14 tensors of FCT / AutoEncoder never do)."""
     dead = set()
