@@ -282,8 +282,17 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         import datetime
-        os.environ["NCCL_DEBUG"] = os.environ.get("HN_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL writes its banner / log lines to fd 1 from C, so fd 1 is pointed
+        # at stderr for the whole run and the JSON line goes to the saved descriptor
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        if "HN_NCCL_DEBUG" in os.environ:
+            os.environ["NCCL_DEBUG"] = os.environ["HN_NCCL_DEBUG"]
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
+    else:
+        json_fd = None
     _lib.call("hn_check_device")
     torch.manual_seed(0)
     model = hybridnet.MODELS[key]().to(dev).train()
@@ -397,9 +406,18 @@ def main():
             cfps, sec, cores = cpu_reference(args.workload, frames, 2, 1)
             result["cpu_baseline"] = {"value": round(cfps, 4), "unit": unit, "cores": cores, "kind": "port",
                                       "sample": f"{frames} frames x 2 timed fwd+bwd passes (oracle port of the reference's PyTorch path, fp32, {sec:.2f} s/pass)"}
-        print(json.dumps(result))
+        if json_fd is None:
+            print(json.dumps(result))
+        else:
+            os.write(json_fd, (json.dumps(result) + "\n").encode())
     if world > 1:
         dist.barrier()
+        # the captured graph holds NCCL's persistent plans: it must die before the communicator does,
+        # or ncclCommDestroy waits for it forever
+        del run, captured
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
 
 
