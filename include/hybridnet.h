@@ -79,6 +79,11 @@ int hn_conv_npad(int Cout);                      /* packed row count            
 int hn_pack_weight(const float* src, void* dst, int N, int Creal, int Cpad, int KH, int KW,
                    long long nmod, long long s_nhi, long long s_n, long long s_c,
                    long long s_kh, long long s_kw, void* stream);
+/* Packed B operand for the input gradient of a stride-2 conv (k in {1,3}, pad k/2; the reference's
+ * Bottleneck conv2 / downsample, pyc:AE_32K:L20-53) run as one stride-1 tcgen05 GEMM over dz with a 2x2
+ * (k3) or 1x1 (k1) window and a pixel-shuffle store: rows (py,px,ci), columns (dh,dw,co).
+ * src = Conv2d weight [Cout][Cin][k][k] fp32; dst = bf16 [hn_conv_npad(4*Cin)][hn_conv_kpad(w,w,Cout)]. */
+int hn_pack_weight_s2dgrad(const float* src, void* dst, int Cout, int Cin, int K, void* stream);
 /* y = act(conv(x1|x2, w) + bias [+ res]); optional per-channel sum / sum-of-squares
  * of the stored (bf16-rounded, pre-activation) values for BatchNorm.            */
 int hn_conv2d_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,

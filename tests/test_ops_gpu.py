@@ -88,6 +88,42 @@ def test_conv2d_fwd_bwd(ops, case):
         assert rel_l2(b.grad, br) < BWD_TOL
 
 
+@pytest.mark.parametrize("cin,cout,k,H,tc", [(128, 128, 3, 32, True), (256, 512, 1, 32, True), (64, 64, 3, 16, True),
+                                             (64, 96, 3, 16, False)])      # K chunk 32 with N = 256: generic kernel
+def test_stride2_input_gradient_runs_on_tcgen05(ops, cin, cout, k, H, tc):
+    """Bottleneck conv2 / downsample (stride 2): dx comes from ONE hn_conv_tc_fwd launch (2x2 window over dz,
+    four output parities on N, pixel-shuffle store) and equals torch's conv input gradient."""
+    import contextlib
+    from hybridnet import _lib
+    B = 2
+    x = _rand(B, cin, H, H, seed=12).requires_grad_(True)
+    w = _rand(cout, cin, k, k, seed=13, scale=1.0 / math.sqrt(cin * k * k)).requires_grad_(True)
+    ref = F.conv2d(x, w, None, 2, k // 2)
+    gy = _rand(*ref.shape, seed=15)
+    ref.backward(gy)
+    xr = x.grad.clone()
+    x.grad = None
+    y = ops.to_nchw(ops.conv2d(ops.to_nhwc(x), w, None, stride=2, pad=k // 2), cout)
+    names = []
+
+    @contextlib.contextmanager
+    def rec(name, args):
+        names.append((name, args[0].pshuf if name.startswith("hn_conv") else 0))
+        yield
+
+    _lib.set_profiler(rec)
+    try:
+        y.backward(gy)
+    finally:
+        _lib.set_profiler(None)
+    if tc:
+        assert ("hn_conv_tc_fwd", cin) in names, names
+        assert not any(n == "hn_conv2d_fwd" for n, _ in names), names
+    else:
+        assert any(n == "hn_conv2d_fwd" for n, _ in names), names
+    assert rel_l2(x.grad, xr) < BWD_TOL
+
+
 def test_conv_virtual_concat_upsample_residual(ops):
     """cat([a,b]) folded into the K loop; nearest-x2 upsample folded into the gather; residual epilogue."""
     B, H = 2, 16

@@ -354,6 +354,46 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, bf16* __restri
   }
 }
 
+// Input gradient of a stride-2 conv (k3 p1 or k1 p0) as ONE stride-1 GEMM over dz with a pixel-shuffle store:
+// dx[2h+py, 2w+px, ci] = sum_{dh,dw,co} dz[h+dh, w+dw, co] * W[co, ci, kh(py,dh), kw(px,dw)],
+// kh(0,0)=1, kh(0,1)=none, kh(1,0)=2, kh(1,1)=0 (k3); k1: only (py,px)=(0,0), no window.
+// Packed as B[(py,px,ci)][(dh,dw,co)] -- 9 of the 16 (parity, tap) blocks are non-zero.
+__global__ void pack_weight_s2dgrad_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int Cout, int Cin,
+                                           int K, int Npad, int Kpad) {
+  const long long total = (long long)Npad * Kpad;
+  const int win = K == 3 ? 2 : 1;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / Kpad), k = (int)(i - (long long)n * Kpad);
+    float v = 0.f;
+    if (n < 4 * Cin && k < win * win * Cout) {
+      const int par = n / Cin, ci = n - par * Cin, py = par >> 1, px = par & 1;
+      const int tap = k / Cout, co = k - tap * Cout, dh = tap / win, dw = tap - dh * win;
+      int kh, kw;
+      if (K == 3) {
+        kh = py == 0 ? (dh == 0 ? 1 : -1) : (dh == 0 ? 2 : 0);
+        kw = px == 0 ? (dw == 0 ? 1 : -1) : (dw == 0 ? 2 : 0);
+      } else {
+        kh = py == 0 ? 0 : -1;
+        kw = px == 0 ? 0 : -1;
+      }
+      if (kh >= 0 && kw >= 0) v = src[(((long long)co * Cin + ci) * K + kh) * K + kw];
+    }
+    dst[i] = __float2bfloat16(v);
+  }
+}
+
+extern "C" int hn_pack_weight_s2dgrad(const float* src, void* dst, int Cout, int Cin, int K, void* stream) {
+  HN_REQUIRE(src && dst && Cout > 0 && Cin > 0 && (K == 1 || K == 3) && Cout % 8 == 0, "pack_weight_s2dgrad: bad args");
+  const int win = K == 3 ? 2 : 1;
+  const int Kpad = hn_conv_kpad(win, win, Cout), Npad = hn_conv_npad(4 * Cin);
+  const long long total = (long long)Npad * Kpad;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  pack_weight_s2dgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(src, (bf16*)dst, Cout, Cin, K, Npad, Kpad);
+  HN_CHECK_LAUNCH("pack_weight_s2dgrad_kernel");
+  return HN_OK;
+}
+
 extern "C" int hn_pack_weight(const float* src, void* dst, int N, int Creal, int Cpad, int KH, int KW,
                               long long nmod, long long s_nhi, long long s_n, long long s_c,
                               long long s_kh, long long s_kw, void* stream) {

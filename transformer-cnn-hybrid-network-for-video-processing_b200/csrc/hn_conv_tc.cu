@@ -562,7 +562,10 @@ bool tc_ok(const HnConv* d) {
   if (d->stride != 1 && d->stride != 2) return false;
   if (d->C1 <= 0 || pick_bkc(d) == 0) return false;
   if (d->H % d->stride || d->W % d->stride || d->OH != d->H / d->stride || d->OW != d->W / d->stride) return false;
-  if (d->pshuf && (d->KH != 1 || d->KW != 1 || d->pshuf % 32 || d->stride != 1)) return false;
+  // pixel-shuffle store: the k2s2 transposed conv (1x1 GEMM, 4 taps on N) and the input gradient of stride-2
+  // convs (2x2 window over dz, pad 0: the row/column past the edge is TMA zero fill; 4 output parities on N)
+  if (d->pshuf && (d->pshuf % 32 || d->stride != 1 || d->KH != d->KW || (d->KH != 1 && (d->KH != 2 || d->pad != 0 || d->dil != 1))))
+    return false;
   int ntot = d->pshuf ? 4 * d->pshuf : d->Cout;
   if (pick_bn(ntot) == 0) return false;
   if (pick_bkc(d) == 32 && pick_bn(ntot) > 64) return false;      // BKC = 32 is built for BN in {32, 64}

@@ -165,6 +165,14 @@ def _packed(w, kind, Cpad):
     src = w.detach()
     assert src.dtype == torch.float32 and src.is_contiguous()
     d0, d1, KH, KW = src.shape
+    if kind == "s2dgrad":       # stride-2 input gradient as a stride-1 GEMM + pixel shuffle (hn_pack_weight_s2dgrad)
+        lib = _lib.load()
+        win = 2 if KH == 3 else 1
+        Kpad = lib.hn_conv_kpad(win, win, d0)
+        buf = torch.empty((lib.hn_conv_npad(4 * d1), Kpad), dtype=torch.bfloat16, device=w.device)
+        call("hn_pack_weight_s2dgrad", src.data_ptr(), buf.data_ptr(), d0, d1, KH, _stream())
+        ent[key] = (buf, Kpad)
+        return ent[key]
     assert kind != "dgradf" or src.is_contiguous()
     big = 1 << 40
     if kind == "fwd":
@@ -208,8 +216,9 @@ def _desc(**kw):
 
 
 def _conv_raw(x1, x2, wp, Kpad, bias, res, *, OH, OW, Cout, KH, KW, stride, pad, dil, mode=0, ups=0,
-              act=ACT_NONE, pshuf=0, stats=None, out=None, H=None, W=None):
-    """One hn_conv2d_fwd launch.  x1/x2 already validated NHWC."""
+              act=ACT_NONE, pshuf=0, stats=None, out=None, H=None, W=None, tc_only=False):
+    """One hn_conv2d_fwd launch.  x1/x2 already validated NHWC.  tc_only: the caller's formulation exists
+    only on the tcgen05 path."""
     x1, ld1 = nhwc(x1)
     B = x1.shape[0]
     H = H if H is not None else x1.shape[1] << ups
@@ -233,6 +242,10 @@ def _conv_raw(x1, x2, wp, Kpad, bias, res, *, OH, OW, Cout, KH, KW, stride, pad,
     s0 = s1 = None
     if stats is not None:
         s0, s1 = stats
+    if tc_only:
+        call("hn_conv_tc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
+             _ptr(s1), _stream())
+        return out
     if res is None and USE_TC and _lib.load().hn_conv_tc_halo_supported(d):
         call("hn_conv_tc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
              _ptr(s1), _stream())
@@ -325,6 +338,19 @@ def _conv_forward(g, x1, x2, weight, bias, res, act, stats=None):
                      pad=g.pad, dil=g.dil, ups=g.ups, act=act, stats=stats)
 
 
+def _s2dgrad_ok(g, dz):
+    """Stride-2 k3p1 / k1p0 conv whose input gradient fits the tcgen05 pixel-shuffle formulation."""
+    if not USE_TC or g.stride != 2 or g.dil != 1 or g.ups or g.KH != g.KW or g.KH not in (1, 3) or g.pad != g.KH // 2:
+        return False
+    if g.H != 2 * g.OH or g.W != 2 * g.OW or g.Cin % 32 or dz.shape[3] != g.Cout or g.Cout % 32:
+        return False
+    dz, ld = nhwc(dz)
+    win = 2 if g.KH == 3 else 1
+    d = _desc(B=dz.shape[0], H=g.OH, W=g.OW, C1=g.Cout, C2=0, ld1=ld, ld2=0, OH=g.OH, OW=g.OW, Cout=g.Cin, ldy=g.Cin,
+              KH=win, KW=win, stride=1, pad=0, dil=1, mode=0, ups=0, act=0, pshuf=g.Cin, ldr=0, Kpad=win * win * g.Cout)
+    return bool(_lib.load().hn_conv_tc_supported(d))
+
+
 def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
     """dz: gradient at the conv output (NHWC, padded channels zero). Returns dx1, dx2, dW."""
     dx1 = dx2 = dw = None
@@ -352,6 +378,13 @@ def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
                 wp, Kpad = _packed(weight, "dgradf", dz.shape[3])
                 full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=g.KH, KW=g.KW,
                                  stride=1, pad=g.dil * (g.KH - 1) - g.pad, dil=g.dil, mode=0, H=g.OH, W=g.OW)
+            elif _s2dgrad_ok(g, dz):
+                # every dx pixel parity is a small stride-1 conv of dz: one tcgen05 GEMM with a 2x2 (k3) / 1x1 (k1)
+                # window, the four parities on N, pixel-shuffle store (no scatter, no zero-fill pass)
+                wp, Kpad = _packed(weight, "s2dgrad", dz.shape[3])
+                win = 2 if g.KH == 3 else 1
+                full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.OH, OW=g.OW, Cout=g.Cin, KH=win, KW=win,
+                                 stride=1, pad=0, dil=1, pshuf=g.Cin, tc_only=True)
             else:
                 wp, Kpad = _packed(weight, "dgrad", dz.shape[3])
                 full = _conv_raw(dz, None, wp, Kpad, None, None, OH=g.H, OW=g.W, Cout=g.Cin, KH=g.KH, KW=g.KW,
