@@ -307,8 +307,11 @@ def main():
     x, y = make_batch(B, 1 + rank, dev)
     xh, yh = make_batch(B, 1 + rank, dev, pinned=True)
 
+    zero_cap = sum(p.numel() for p in model.parameters()) + (1 << 18)
+
     def step(xd, yd):
         arena.zero_grad()
+        ops.begin_step(dev, zero_cap)           # all zero-initialised fp32 scratch of the step: one memset
         ops.invalidate_packed()                 # weights change every step in training: pay for the repack
         out = model(xd)
         loss = loss_fn(kind, out, xd, yd)

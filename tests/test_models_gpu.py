@@ -344,8 +344,11 @@ def test_captured_step_matches_eager_and_redraws_dropout():
     x = torch.rand(2, 3, 64, 64, device=dev)
     y = (torch.rand(2, 1, 64, 64, device=dev) > 0.5).float()
 
+    cap_floats = sum(p.numel() for p in m.parameters()) + (1 << 16)
+
     def step(xd, yd):
         arena.zero_grad()
+        ops.begin_step(dev, cap_floats)         # zero pool: one memset for every fp32 accumulator of the step
         ops.invalidate_packed()
         out = m(xd)
         p, t = out[:, 0].reshape(-1), yd[:, 0].reshape(-1)
@@ -397,6 +400,7 @@ def test_captured_step_matches_eager_and_redraws_dropout():
 
     def fstep(xd, yd):
         fa.zero_grad()
+        ops.begin_step(dev, sum(p.numel() for p in f.parameters()) + (1 << 16))
         out = f(xd)
         loss = out.mean()
         loss.backward()
@@ -405,3 +409,4 @@ def test_captured_step_matches_eager_and_redraws_dropout():
     fc = parallel.CapturedStep(fstep, x, y, warmup=1)
     losses = {round(float(fc()), 7) for _ in range(4)}
     assert len(losses) == 4, losses
+    ops.end_zero_pool()

@@ -71,9 +71,48 @@ def _new(B, H, W, C, like, zero=False):
     return f((B, H, W, C), dtype=torch.bfloat16, device=like.device)
 
 
+# Zero-initialised fp32 scratch (BatchNorm sums, bias/weight-gradient accumulators: everything the kernels
+# add into with atomics).  Eagerly each is its own torch fill launch -- ~250 two-microsecond launches per
+# Autoencoder32K step.  A training loop that calls ``begin_step`` once per step gets them as slices of ONE
+# pool cleared by ONE memset instead.  Contract: tensors handed out from the pool are dead by the next
+# ``begin_step`` (gradients are accumulated into ``p.grad`` / the GradArena before the step ends); without
+# ``begin_step`` nothing changes (plain torch.zeros).
+_zero_pool = {"buf": None, "off": 0, "live": False}
+
+
+def begin_step(device, capacity=None):
+    """Clear the zero pool (one memset).  capacity (floats) defaults to the previous size; the first call
+    must give it (e.g. total parameter count + 64k)."""
+    zp = _zero_pool
+    device = torch.device(device)
+    if zp["buf"] is None or zp["buf"].device != device or (capacity and zp["buf"].numel() < capacity):
+        if capacity is None:
+            raise RuntimeError("hybridnet.ops.begin_step: first call needs a capacity")
+        zp["buf"] = torch.empty(int(capacity), dtype=torch.float32, device=device)
+    zp["buf"].zero_()
+    zp["off"], zp["live"] = 0, True
+
+
+def end_zero_pool():
+    """Back to one torch.zeros per request (e.g. before code that keeps gradients across steps)."""
+    _zero_pool["live"] = False
+
+
 def _f32(n, like, zero=True):
-    f = torch.zeros if zero else torch.empty
-    return f(n, dtype=torch.float32, device=like.device)
+    if zero:
+        zp = _zero_pool
+        shape = (n,) if isinstance(n, int) else tuple(n)
+        cnt = 1
+        for d in shape:
+            cnt *= d
+        if zp["live"] and zp["buf"].device == like.device:
+            end = zp["off"] + (cnt + 3) // 4 * 4            # 16-byte aligned slices (vector reductions)
+            if end <= zp["buf"].numel():
+                t = zp["buf"][zp["off"]:zp["off"] + cnt].view(shape)
+                zp["off"] = end
+                return t
+        return torch.zeros(shape, dtype=torch.float32, device=like.device)
+    return torch.empty(n, dtype=torch.float32, device=like.device)
 
 
 def _ptr(t):
@@ -359,7 +398,7 @@ def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
     C1 = x1.shape[3]
     C2 = x2.shape[3] if x2 is not None else 0
     if need_dw:
-        dw = torch.zeros_like(weight, dtype=torch.float32)
+        dw = _f32(tuple(weight.shape), weight)
         if g.transposed:
             # dW[ci][co][kh][kw] = sum_p x[p,ci] * dy[2p+(kh,kw), co]: wgrad of the k2s2 conv dy -> x
             _wgrad_raw(dz, None, x1, dw, Creal=g.Cout, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
@@ -488,7 +527,7 @@ class _BnActFn(torch.autograd.Function):
                 rm, rv = _pad_vec(running_mean, Cp), _pad_vec(running_var, Cp, 1.0)
             call("hn_bn_finalize", s0.data_ptr(), s1.data_ptr(), P, Cp, eps, momentum, mean.data_ptr(),
                  rstd.data_ptr(), _ptr(rm), _ptr(rv), _stream())
-            if rm is not None:
+            if rm is not None and rm.data_ptr() != running_mean.data_ptr():      # padded copies only (C % 8 != 0)
                 running_mean.copy_(rm[:C])
                 running_var.copy_(rv[:C])
         else:
@@ -522,7 +561,7 @@ class _BnActFn(torch.autograd.Function):
                  rstd.data_ptr(), gam.data_ptr(), bet.data_ptr(), s1.data_ptr(), s2.data_ptr(), P, Cp, lddy, ldz,
                  Cp, 1 if ctx.training else 0, _stream())
             C = ctx.C
-            return (dx, s2[:C].clone(), s1[:C].clone(), None, None, None, None, None, None, None, None, None)
+            return (dx, s2[:C], s1[:C], None, None, None, None, None, None, None, None, None)
         need_dz_buf = ctx.act != ACT_NONE
         dz = _new(B, H, W, Cp, z) if need_dz_buf else dy
         lddz = Cp if need_dz_buf else lddy
@@ -536,7 +575,7 @@ class _BnActFn(torch.autograd.Function):
         call("hn_bn_bwd_apply", dz.data_ptr(), z.data_ptr(), dx.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
              gam.data_ptr(), s1.data_ptr(), s2.data_ptr(), P, Cp, lddz, ldz, Cp, 1 if ctx.training else 0, _stream())
         C = ctx.C
-        return (dx, s2[:C].clone(), s1[:C].clone(), dz if ctx.has_res else None,
+        return (dx, s2[:C], s1[:C], dz if ctx.has_res else None,
                 None, None, None, None, None, None, None, None)
 
 
@@ -572,7 +611,7 @@ class _ConvStatsFn(torch.autograd.Function):
         # gradient, whose per-channel sum vanishes identically (sum_p [dz - mean(dz) - xhat*mean(dz*xhat)]
         # = 0); the reference's autograd gets fp32 round-off around 0.  No reduction pass is spent on it.
         dz, _ = _act_bwd(dy, None, ACT_NONE, False)
-        dbias = torch.zeros(g.Cout, dtype=torch.float32, device=dz.device) if (ctx.has_bias and need[3]) else None
+        dbias = _f32(g.Cout, dz) if (ctx.has_bias and need[3]) else None
         dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2])
         return (dx1 if need[0] else None, dx2 if need[1] else None, dw, dbias, None, None, None, None, None)
 
