@@ -174,6 +174,19 @@ class KernelProfiler:
         return agg
 
 
+def ncu_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full
+    capture of this workload (profiles/*_traffic.json, newest first); (None, None) when there is none."""
+    import glob
+    for f in sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "*_traffic.json")), reverse=True):
+        try:
+            d = json.load(open(f))
+            return d[workload][kernel]["traffic_bytes_per_launch"], d["source"]
+        except (KeyError, ValueError, OSError):
+            continue
+    return None, None
+
+
 def roofline_from(agg, steps, peaks):
     if any("[" in k for k in agg):            # --kernel-detail rows: the roofline object is per kernel, not per geometry
         merged = {}
@@ -384,6 +397,7 @@ def main():
         _lib.set_profiler(None)
         agg = prof.table()
         roof = roofline_from(agg, psteps, peaks)
+        roof["traffic"], roof["traffic_source"] = ncu_traffic(args.workload, roof["kernel"])
         if args.kernel_table:
             tot = sum(a["ms"] for a in agg.values())
             for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
