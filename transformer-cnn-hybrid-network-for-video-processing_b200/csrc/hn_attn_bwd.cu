@@ -77,17 +77,21 @@ __global__ void __launch_bounds__(NWARP * 32) attn_bwd_dq_kernel(
     cp_async_wait<1>();
     __syncthreads();
     float ds[TILE / 8][4];
+    const bool ragged = (kt + 1) * TILE > N;
 #pragma unroll
     for (int j = 0; j < TILE / 8; ++j) {
       float s[4] = {0.f, 0.f, 0.f, 0.f}, dp[4] = {0.f, 0.f, 0.f, 0.f};
       mma_over_d<D, DP>(s, qa, sK[cur], j, lane);
       mma_over_d<D, DP>(dp, doa, sV[cur], j, lane);
-      int key = kt * TILE + j * 8 + 2 * t;
-      bool k0 = key < N, k1 = (key + 1) < N;
-      float p0 = k0 ? ex2(s[0] * sl2 - l2[0]) : 0.f;
-      float p1 = k1 ? ex2(s[1] * sl2 - l2[0]) : 0.f;
-      float p2 = k0 ? ex2(s[2] * sl2 - l2[1]) : 0.f;
-      float p3 = k1 ? ex2(s[3] * sl2 - l2[1]) : 0.f;
+      float p0 = ex2(s[0] * sl2 - l2[0]);
+      float p1 = ex2(s[1] * sl2 - l2[0]);
+      float p2 = ex2(s[2] * sl2 - l2[1]);
+      float p3 = ex2(s[3] * sl2 - l2[1]);
+      if (ragged) {      // warp-uniform: only the last key tile of an N that is not a multiple of 64
+        int key = kt * TILE + j * 8 + 2 * t;
+        if (key >= N) p0 = p2 = 0.f;
+        if (key + 1 >= N) p1 = p3 = 0.f;
+      }
       ds[j][0] = p0 * (dp[0] - dl[0]);
       ds[j][1] = p1 * (dp[1] - dl[0]);
       ds[j][2] = p2 * (dp[2] - dl[1]);
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(NWARP * 32) attn_bwd_dkv_kernel(
   constexpr int TB = TILE * DP * 2;
   __shared__ __align__(128) uint8_t sQ[2][TB];
   __shared__ __align__(128) uint8_t sDO[2][TB];
-  __shared__ float sL[2][TILE], sDl[2][TILE];
+  __shared__ __align__(8) float sL[2][TILE], sDl[2][TILE];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int head = blockIdx.y, b = blockIdx.z;
@@ -173,9 +177,10 @@ __global__ void __launch_bounds__(NWARP * 32) attn_bwd_dkv_kernel(
       float s[4] = {0.f, 0.f, 0.f, 0.f}, dp[4] = {0.f, 0.f, 0.f, 0.f};
       mma_over_d<D, DP>(s, ka, sQ[cur], j, lane);      // S^T tile: rows = keys, cols = queries
       mma_over_d<D, DP>(dp, va, sDO[cur], j, lane);    // dP^T
-      int qc = j * 8 + 2 * t;
-      float la = sL[cur][qc], lb = sL[cur][qc + 1];
-      float da = sDl[cur][qc], db = sDl[cur][qc + 1];
+      const int qc = j * 8 + 2 * t;
+      const float2 lv = *reinterpret_cast<const float2*>(&sL[cur][qc]);
+      const float2 dv2 = *reinterpret_cast<const float2*>(&sDl[cur][qc]);
+      const float la = lv.x, lb = lv.y, da = dv2.x, db = dv2.y;
       pt[j][0] = ex2(s[0] * sl2 - la);
       pt[j][1] = ex2(s[1] * sl2 - lb);
       pt[j][2] = ex2(s[2] * sl2 - la);
