@@ -223,7 +223,7 @@ def roofline_from(agg, steps, peaks):
 # ---------------------------------------------------------------------------------------------
 # reference arm / cpu baseline: the oracle (CPU restatement of the reference's PyTorch path)
 # ---------------------------------------------------------------------------------------------
-def cpu_reference(workload, frames, steps, warmup):
+def cpu_reference(workload, frames, steps, warmup, infer=False):
     """fwd+bwd of the reference arithmetic (oracle/nets.py, fp32, all host cores) on `frames` frames."""
     from oracle import nets
     key, _, kind, _ = WORKLOADS[workload]
@@ -234,15 +234,19 @@ def cpu_reference(workload, frames, steps, warmup):
     params = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running" not in k and not frozen(k) else v)
               for k, v in sd.items()}
     x, y = make_batch(frames, 1, "cpu")
-    ctx = nets.Ctx(training=True, dropout="on")
+    ctx = nets.Ctx(training=not infer, dropout="off" if infer else "on")
     times = []
     for i in range(warmup + steps):
         for p in params.values():
             if p.requires_grad:
                 p.grad = None
         t0 = time.perf_counter()
-        out = nets.FORWARDS[key](params, x, ctx)
-        loss_fn(kind, out, x, y).backward()
+        if infer:
+            with torch.no_grad():
+                nets.FORWARDS[key](params, x, ctx)
+        else:
+            out = nets.FORWARDS[key](params, x, ctx)
+            loss_fn(kind, out, x, y).backward()
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     sec = sum(times) / len(times)
@@ -261,6 +265,8 @@ def main():
     ap.add_argument("--no-dropout", action="store_true")
     ap.add_argument("--kernel-table", action="store_true", help="print the per-kernel time table to stderr")
     ap.add_argument("--kernel-detail", action="store_true", help="per conv geometry rows in the kernel table")
+    ap.add_argument("--infer", action="store_true", help="eval-mode forward only (BASELINE configs[3] inference leg); "
+                    "e2e copies the whole output back to pinned host memory")
     ap.add_argument("--no-graph", action="store_true", help="issue every kernel eagerly instead of replaying the captured step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
@@ -271,6 +277,8 @@ def main():
     key, B0, kind, cfg_name = WORKLOADS[args.workload]
     B = args.batch or B0
     metric, unit = "train frames/sec (fwd+bwd, 256x256)", "frames/s"
+    if args.infer:
+        metric = "inference frames/sec (eval-mode fwd, 256x256)"
     config = {"workload": cfg_name, "frames_per_gpu": B, "global_batch": B * world, "frame": "3x256x256 fp32 in [0,1)",
               "parallelism": f"dp{world}" if world > 1 else "single", "l2": "activations per step >> 126 MB L2 (no flush needed)"}
 
@@ -279,8 +287,8 @@ def main():
             return
         frames = 2 if key in ("fct", "ae32k_image", "latent2mask", "i2i2m") else 4
         steps = max(1, min(args.steps, 3))
-        fps, sec, cores = cpu_reference(args.workload, frames, steps, 1)
-        sample = f"{frames} frames x {steps} timed fwd+bwd passes of the same net (oracle port of the reference's PyTorch path, fp32)"
+        fps, sec, cores = cpu_reference(args.workload, frames, steps, 1, args.infer)
+        sample = f"{frames} frames x {steps} timed {'fwd' if args.infer else 'fwd+bwd'} passes of the same net (oracle port of the reference's PyTorch path, fp32)"
         print(json.dumps({"impl": "reference", "metric": metric, "value": round(fps, 4), "unit": unit, "n_gpus": args.gpus,
                           "steps": steps, "warmup": 1, "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
@@ -309,6 +317,8 @@ def main():
     _lib.call("hn_check_device")
     torch.manual_seed(0)
     model = hybridnet.MODELS[key]().to(dev).train()
+    if args.infer:
+        model.eval()
     if args.no_dropout:
         for m in model.modules():
             if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
@@ -322,7 +332,14 @@ def main():
 
     zero_cap = sum(p.numel() for p in model.parameters()) + (1 << 18)
 
+    def infer_step(xd, yd):
+        with torch.no_grad():
+            out = model(xd)
+        return out[-1] if isinstance(out, tuple) else out
+
     def step(xd, yd):
+        if args.infer:
+            return infer_step(xd, yd)
         arena.zero_grad()
         ops.begin_step(dev, zero_cap)           # all zero-initialised fp32 scratch of the step: one memset
         ops.invalidate_packed()                 # weights change every step in training: pay for the repack
@@ -368,8 +385,15 @@ def main():
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     last = 0.0
+    out_host = None
     for _ in range(args.steps):
-        if captured:
+        if args.infer:                             # the whole output (mask / reconstruction) comes back to the host
+            out = captured(xh, yh) if captured else step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True))
+            if out_host is None:
+                out_host = torch.empty(out.shape, dtype=out.dtype).pin_memory()
+            out_host.copy_(out)
+            last = float(out_host.view(-1)[0])
+        elif captured:
             last = float(captured(xh, yh).item())  # pinned host -> static device buffers, replay, loss -> host
         else:
             xd = xh.to(dev, non_blocking=True)
@@ -405,7 +429,7 @@ def main():
                       f"{a['flops'] / max(a['ms'], 1e-9) / 1e9:8.1f} TFLOP/s {a['bytes'] / max(a['ms'], 1e-9) / 1e6:8.0f} GB/s",
                       file=sys.stderr)
         from oracle.nets import GFLOP_PER_FRAME
-        gf = GFLOP_PER_FRAME[key][1]
+        gf = GFLOP_PER_FRAME[key][0 if args.infer else 1]
         fps = B * world * args.steps / (ms / 1e3)
         fps_e2e = B * world * args.steps / (ms_e2e / 1e3)
         result = {"metric": metric, "value": round(fps, 2), "unit": unit, "n_gpus": world, "steps": args.steps,
@@ -413,16 +437,17 @@ def main():
                   "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
                   "clocks": clocks.summary(),
                   "e2e": {"value": round(fps_e2e, 2), "unit": unit, "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4),
-                          "d2h_bytes_per_step": 4, "last_loss": round(last, 5)},
+                          "d2h_bytes_per_step": int(out_host.numel() * out_host.element_size()) if args.infer else 4,
+                          "last_loss": round(last, 5)},
                   "gpu_launches": launches,
-                  "model_tensor_roofline": {"GFLOP_per_frame_fwd_bwd": gf, "achieved_TFLOPs": round(fps / world * gf / 1e3, 2),
+                  "model_tensor_roofline": {"GFLOP_per_frame_fwd" if args.infer else "GFLOP_per_frame_fwd_bwd": gf, "achieved_TFLOPs": round(fps / world * gf / 1e3, 2),
                                             "frac_of_sustained_bf16": round(fps / world * gf / 1e3 / peaks["tensor"], 4)},
                   "roofline": roof}
         if world == 1 and not args.no_cpu_baseline:
             frames = 2
-            cfps, sec, cores = cpu_reference(args.workload, frames, 2, 1)
+            cfps, sec, cores = cpu_reference(args.workload, frames, 2, 1, args.infer)
             result["cpu_baseline"] = {"value": round(cfps, 4), "unit": unit, "cores": cores, "kind": "port",
-                                      "sample": f"{frames} frames x 2 timed fwd+bwd passes (oracle port of the reference's PyTorch path, fp32, {sec:.2f} s/pass)"}
+                                      "sample": f"{frames} frames x 2 timed {'fwd' if args.infer else 'fwd+bwd'} passes (oracle port of the reference's PyTorch path, fp32, {sec:.2f} s/pass)"}
         if json_fd is None:
             print(json.dumps(result))
         else:
