@@ -326,7 +326,7 @@ def main():
     ops.manual_seed(1234 + rank)
     dead = parallel.used_parameter_names(key)
     used = {n for n, p in model.named_parameters() if p.requires_grad and n not in dead}
-    arena = parallel.GradArena(model, used=used, buckets=4)
+    arena = parallel.GradArena(model, used=used, buckets=4).direct()     # kernels reduce dW / BN grads straight into the arena
     x, y = make_batch(B, 1 + rank, dev)
     xh, yh = make_batch(B, 1 + rank, dev, pinned=True)
 

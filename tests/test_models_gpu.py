@@ -393,6 +393,22 @@ def test_captured_step_matches_eager_and_redraws_dropout():
     l_c, g_c = run(cap_eval, x, y)
     assert abs(l_e - l_c) < 1e-6
     assert rel(g_c, g_e) < 1e-3
+    # gradient sink: conv-weight / BatchNorm-parameter gradients reduced by the kernels straight into the arena
+    # (no per-tensor zero fill, no AccumulateGrad add) must equal the autograd-accumulated ones
+    try:
+        arena.direct(True)
+        l_d, g_d = run(step, x, y)
+        assert abs(l_e - l_d) < 1e-6
+        assert rel(g_d, g_e) < 1e-3, rel(g_d, g_e)
+        cap_direct = parallel.CapturedStep(step, x, y, warmup=1)
+        assert cap_direct.launches == cap_eval.launches
+        l_dc, g_dc = run(cap_direct, x, y)
+        assert rel(g_dc, g_e) < 1e-3
+        m.train()
+        l_t, g_t = run(step, x, y)          # train-mode BN: inside the eager noise band measured above
+        assert rel(g_t, g_e1) < 3 * noise, (rel(g_t, g_e1), noise)
+    finally:
+        arena.direct(False)
 
     # dropout: FCT has Dropout(0.3)/(0.1) on the path; replays of one graph must not repeat the mask
     f = hybridnet.FCT().to(dev).train()

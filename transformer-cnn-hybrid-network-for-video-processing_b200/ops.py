@@ -377,6 +377,31 @@ def _conv_forward(g, x1, x2, weight, bias, res, act, stats=None):
                      pad=g.pad, dil=g.dil, ups=g.ups, act=act, stats=stats)
 
 
+# Gradient sink: a training loop that owns the gradient storage (parallel.GradArena) registers
+# ``sink(param_data_ptr, numel) -> fp32 accumulation target | None`` and ``done(param_data_ptr)``.  The weight- and
+# BatchNorm-parameter gradients are then reduced by the kernels DIRECTLY into that storage (it is zeroed once per
+# step) and autograd gets None for them: no per-tensor zero fill, no per-tensor AccumulateGrad add launch.
+_grad_sink = {"sink": None, "done": None}
+
+
+def set_grad_sink(sink, done):
+    _grad_sink["sink"], _grad_sink["done"] = sink, done
+
+
+def _sink_for(t):
+    f = _grad_sink["sink"]
+    return f(t.data_ptr(), t.numel()) if (f is not None and t is not None) else None
+
+
+def _sink_for_ptr(ptr, numel):
+    f = _grad_sink["sink"]
+    return f(ptr, numel) if (f is not None and ptr) else None
+
+
+def _sink_done(ptr):
+    _grad_sink["done"](ptr)
+
+
 def _s2dgrad_ok(g, dz):
     """Stride-2 k3p1 / k1p0 conv whose input gradient fits the tcgen05 pixel-shuffle formulation."""
     if not USE_TC or g.stride != 2 or g.dil != 1 or g.ups or g.KH != g.KW or g.KH not in (1, 3) or g.pad != g.KH // 2:
@@ -397,8 +422,10 @@ def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
     B = x1.shape[0]
     C1 = x1.shape[3]
     C2 = x2.shape[3] if x2 is not None else 0
+    sunk = None
     if need_dw:
-        dw = _f32(tuple(weight.shape), weight)
+        sunk = _sink_for(weight)
+        dw = sunk.view(weight.shape) if sunk is not None else _f32(tuple(weight.shape), weight)
         if g.transposed:
             # dW[ci][co][kh][kw] = sum_p x[p,ci] * dy[2p+(kh,kw), co]: wgrad of the k2s2 conv dy -> x
             _wgrad_raw(dz, None, x1, dw, Creal=g.Cout, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
@@ -437,6 +464,9 @@ def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
                 full = small
             dx1 = full[..., :C1] if C2 else full
             dx2 = full[..., C1:] if C2 else None
+    if sunk is not None:
+        _sink_done(weight.data_ptr())
+        dw = None
     return dx1, dx2, dw
 
 
@@ -540,6 +570,8 @@ class _BnActFn(torch.autograd.Function):
         call("hn_bn_apply", z.data_ptr(), _ptr(res), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gam.data_ptr(),
              bet.data_ptr(), P, Cp, ldz, ldr, Cp, act, _stream())
         ctx.act, ctx.training, ctx.C, ctx.has_res = act, training, C, res is not None
+        direct = C == Cp and gamma.requires_grad and beta.requires_grad and gamma.dtype == torch.float32
+        ctx.gptr, ctx.bptr = (gamma.data_ptr(), beta.data_ptr()) if direct else (0, 0)
         ctx.maskz = act == ACT_RELU and res is None      # ReLU mask re-derived from z in backward
         ctx.save_for_backward(z, y if (act != ACT_NONE and not ctx.maskz) else None, mean, rstd, gam,
                               bet if ctx.maskz else None)
@@ -552,7 +584,11 @@ class _BnActFn(torch.autograd.Function):
         z, ldz = nhwc(z)
         B, H, W, Cp = z.shape
         P = B * H * W
-        s1, s2 = _f32(Cp, z), _f32(Cp, z)
+        # per-channel sums of the two reductions ARE dbeta / dgamma: reduce straight into the gradient sink
+        k1 = _sink_for_ptr(ctx.bptr, Cp)
+        k2 = _sink_for_ptr(ctx.gptr, Cp) if k1 is not None else None
+        sunk = k1 is not None and k2 is not None
+        s1, s2 = (k1, k2) if sunk else (_f32(Cp, z), _f32(Cp, z))
         if ctx.maskz:
             call("hn_bn_relu_bwd_reduce", dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
                  gam.data_ptr(), bet.data_ptr(), P, Cp, lddy, ldz, s1.data_ptr(), s2.data_ptr(), _stream())
@@ -561,6 +597,10 @@ class _BnActFn(torch.autograd.Function):
                  rstd.data_ptr(), gam.data_ptr(), bet.data_ptr(), s1.data_ptr(), s2.data_ptr(), P, Cp, lddy, ldz,
                  Cp, 1 if ctx.training else 0, _stream())
             C = ctx.C
+            if sunk:
+                _sink_done(ctx.gptr)
+                _sink_done(ctx.bptr)
+                return (dx, None, None, None, None, None, None, None, None, None, None, None)
             return (dx, s2[:C], s1[:C], None, None, None, None, None, None, None, None, None)
         need_dz_buf = ctx.act != ACT_NONE
         dz = _new(B, H, W, Cp, z) if need_dz_buf else dy
@@ -575,6 +615,10 @@ class _BnActFn(torch.autograd.Function):
         call("hn_bn_bwd_apply", dz.data_ptr(), z.data_ptr(), dx.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
              gam.data_ptr(), s1.data_ptr(), s2.data_ptr(), P, Cp, lddz, ldz, Cp, 1 if ctx.training else 0, _stream())
         C = ctx.C
+        if sunk:
+            _sink_done(ctx.gptr)
+            _sink_done(ctx.bptr)
+            return (dx, None, None, dz if ctx.has_res else None, None, None, None, None, None, None, None, None)
         return (dx, s2[:C], s1[:C], dz if ctx.has_res else None,
                 None, None, None, None, None, None, None, None)
 
@@ -600,6 +644,7 @@ class _ConvStatsFn(torch.autograd.Function):
         ctx.g, ctx.has_bias = g, bias is not None
         ctx.save_for_backward(x1, x2, weight)
         ctx.mark_non_differentiable(s0, s1)
+        ctx.set_materialize_grads(False)      # or autograd fills two zero vectors per layer for the unused s0/s1 grads
         return y, s0, s1
 
     @staticmethod

@@ -53,9 +53,36 @@ class GradArena:
         self.comm = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
         self.works = []
         self._attach()
+        self._hooks = [self._make_hook(i) for i in range(len(self.params))]
         if self.world > 1:
             for i, p in enumerate(self.params):
-                p.register_post_accumulate_grad_hook(self._make_hook(i))
+                p.register_post_accumulate_grad_hook(self._hooks[i])
+        self._by_ptr = {p.data_ptr(): i for i, p in enumerate(self.params)}
+
+    def direct(self, on=True):
+        """Let the kernels reduce weight / BatchNorm-parameter gradients straight into the arena
+        (``ops.set_grad_sink``): no per-tensor zero fill and no AccumulateGrad add launch.  Valid while the
+        arena is zeroed once per step (``zero_grad``) -- the sums land on zeros.  The bucket bookkeeping that
+        the post-accumulate hooks do is driven by the sink's ``done`` callback instead."""
+        from . import ops
+        if not on:
+            ops.set_grad_sink(None, None)
+            return self
+
+        def sink(ptr, numel):
+            i = self._by_ptr.get(ptr)
+            if i is None:
+                return None
+            s, e = self.slices[i]
+            return self.arena[s:e] if e - s == numel else None
+
+        def done(ptr):
+            i = self._by_ptr[ptr]
+            if self.world > 1:
+                self._hooks[i](None)
+
+        ops.set_grad_sink(sink, done)
+        return self
 
     def _attach(self):
         for p, (s, e) in zip(self.params, self.slices):
