@@ -142,7 +142,8 @@ int hn_bn_stats(const void* x, long long P, int C, int ld, float* sum, float* sq
 /* mean/rstd from sums; running stats update with momentum and unbiased var      */
 int hn_bn_finalize(const float* sum, const float* sqsum, long long count, int C, float eps,
                    float momentum, float* mean, float* rstd, float* running_mean,
-                   float* running_var, void* stream);
+                   float* running_var, long long* num_batches_tracked /* device i64 or NULL: += 1 */,
+                   void* stream);
 /* y = act((x-mean)*rstd*gamma+beta [+ res]) */
 int hn_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd,
                 const float* gamma, const float* beta, long long P, int C, int ldx, int ldr,

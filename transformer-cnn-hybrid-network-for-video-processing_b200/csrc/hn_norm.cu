@@ -143,8 +143,10 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const bf16* __restrict__ 
 }
 __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq, long long count, int C,
                                    float eps, float momentum, float* __restrict__ mean, float* __restrict__ rstd,
-                                   float* __restrict__ rmean, float* __restrict__ rvar) {
+                                   float* __restrict__ rmean, float* __restrict__ rvar,
+                                   long long* __restrict__ num_batches) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && num_batches) *num_batches += 1;      // BatchNorm2d.num_batches_tracked (one launch less per layer)
   if (c >= C) return;
   double m = (double)sum[c] / (double)count;
   double v = (double)sq[c] / (double)count - m * m;
@@ -327,10 +329,10 @@ extern "C" int hn_bn_stats(const void* x, long long P, int C, int ld, float* sum
   HN_CHECK_LAUNCH("bn_stats");
   return HN_OK;
 }
-extern "C" int hn_bn_finalize(const float* sum, const float* sqsum, long long count, int C, float eps, float momentum, float* mean, float* rstd, float* running_mean, float* running_var, void* stream) {
+extern "C" int hn_bn_finalize(const float* sum, const float* sqsum, long long count, int C, float eps, float momentum, float* mean, float* rstd, float* running_mean, float* running_var, long long* num_batches_tracked, void* stream) {
   HN_REQUIRE(sum && sqsum && mean && rstd && count > 0 && C > 0, "bn_finalize: bad args");
   HN_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_finalize: running stats come in pairs");
-  bn_finalize_kernel<<<hn_cdiv(C, 128), 128, 0, ST>>>(sum, sqsum, count, C, eps, momentum, mean, rstd, running_mean, running_var);
+  bn_finalize_kernel<<<hn_cdiv(C, 128), 128, 0, ST>>>(sum, sqsum, count, C, eps, momentum, mean, rstd, running_mean, running_var, num_batches_tracked);
   HN_CHECK_LAUNCH("bn_finalize");
   return HN_OK;
 }

@@ -556,7 +556,7 @@ class _BnActFn(torch.autograd.Function):
             if running_mean is not None:
                 rm, rv = _pad_vec(running_mean, Cp), _pad_vec(running_var, Cp, 1.0)
             call("hn_bn_finalize", s0.data_ptr(), s1.data_ptr(), P, Cp, eps, momentum, mean.data_ptr(),
-                 rstd.data_ptr(), _ptr(rm), _ptr(rv), _stream())
+                 rstd.data_ptr(), _ptr(rm), _ptr(rv), _ptr(count_real), _stream())
             if rm is not None and rm.data_ptr() != running_mean.data_ptr():      # padded copies only (C % 8 != 0)
                 running_mean.copy_(rm[:C])
                 running_var.copy_(rv[:C])
@@ -624,9 +624,10 @@ class _BnActFn(torch.autograd.Function):
 
 
 def bn_act(z, gamma, beta, running_mean, running_var, training, *, res=None, momentum=0.1, eps=1e-5, act="none",
-           stats=None):
+           stats=None, num_batches_tracked=None):
+    """num_batches_tracked: the module's int64 counter; when given (training) the finalize kernel bumps it."""
     return _BnActFn.apply(z, gamma, beta, res, running_mean, running_var, training, momentum, eps, ACTS[act], stats,
-                          None)
+                          num_batches_tracked if training else None)
 
 
 class _ConvStatsFn(torch.autograd.Function):
@@ -669,13 +670,11 @@ def conv_bn_act(x, weight, bias, bn, *, x2=None, res=None, stride=1, pad=1, dil=
     if training:
         z, s0, s1 = _ConvStatsFn.apply(x, x2, weight, bias, stride, pad, dil, ups, transposed)
         stats = (s0, s1)
-        if bn.num_batches_tracked is not None:
-            bn.num_batches_tracked.add_(1)
     else:
         z = conv2d(x, weight, bias, x2=x2, stride=stride, pad=pad, dil=dil, ups=ups, transposed=transposed)
         stats = None
     return bn_act(z, bn.weight, bn.bias, bn.running_mean, bn.running_var, training, res=res, momentum=bn.momentum,
-                  eps=bn.eps, act=act, stats=stats)
+                  eps=bn.eps, act=act, stats=stats, num_batches_tracked=bn.num_batches_tracked)
 
 
 # ----------------------------------------------------------------------------
