@@ -228,9 +228,13 @@ int hn_conv_wgrad_sc(const HnConv* d, const void* x1, const void* x2, const void
  * C2%64==0, Cout>=64 and 64-pixel tileable output maps.  Per tap: D[Cout,Cin] = dz^T x_tap with both
  * operands MN-major straight from TMA boxes, accumulators in TMEM, split over pixels + fp32 atomics. */
 int hn_conv_wgrad_tc_supported(const HnConv* d);
+/* workspace (fp32 elements, caller-owned, uninitialised) = hn_conv_wgrad_tc_workspace(d, s_c): with it the
+ * per-split partial sums are stored and reduced by a second pass instead of scalar atomics (3x3 weights);
+ * NULL / too small / s_c == 1 (1x1 weights, vector reductions): atomics straight into dw.           */
+long long hn_conv_wgrad_tc_workspace(const HnConv* d, long long s_c);
 int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2, const void* dy, float* dw,
                      int Creal, long long s_n, long long s_c, long long s_kh, long long s_kw,
-                     void* stream);
+                     float* workspace, long long workspace_floats, void* stream);
 
 /* ---- fused multi-tensor AdamW on a flat fp32 arena (FCT.py:305,338) --------- */
 int hn_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,

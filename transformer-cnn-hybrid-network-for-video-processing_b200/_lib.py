@@ -72,10 +72,12 @@ SIGNATURES = {
     "hn_conv_wgrad_sc_supported": [POINTER(HnConv)],
     "hn_conv_wgrad_sc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _P],
     "hn_conv_wgrad_tc_supported": [POINTER(HnConv)],
-    "hn_conv_wgrad_tc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _P],
+    "hn_conv_wgrad_tc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _FP, _L, _P],
+    "hn_conv_wgrad_tc_workspace": [POINTER(HnConv), _L],
     "hn_adamw_step": [_FP, _FP, _FP, _FP, _L, _F, _F, _F, _F, _F, _I, _F, _P],
 }
 
+_LONG_RESULT = {"hn_conv_wgrad_tc_workspace"}
 _lib = None
 
 
@@ -95,7 +97,7 @@ def load():
     for name, args in SIGNATURES.items():
         fn = getattr(lib, name)        # AttributeError => header/library mismatch
         fn.argtypes = args
-        fn.restype = c_int
+        fn.restype = c_longlong if name in _LONG_RESULT else c_int
     _lib = lib
     return lib
 

@@ -32,6 +32,8 @@ struct WgTc {
   int mblocks, ct1, ct2;                    // n-blocks of 256, c-tiles (<=256) in x1 / x2
   long long s_n, s_c, s_kh, s_kw;
   float* dw;
+  float* ws;                                // optional partial-sum workspace [splits][taps][Cout][Ctot] (two-stage reduce)
+  int Ctot;
 };
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -97,6 +99,20 @@ __device__ __forceinline__ uint64_t make_mn_desc(uint32_t smem_addr, uint32_t lb
   d |= (uint64_t)1 << 46;
   d |= (uint64_t)2 << 61;
   return d;
+}
+
+// one lane of a converged warp (see hn_conv_tc.cu: issuing tcgen05.mma from inside `if (lane == 0)` makes ptxas
+// wrap every UTCHMMA in an elect loop)
+__device__ __forceinline__ bool wg_elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, P;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
 }
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -168,15 +184,17 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      // M = 128, N = ncols, A and B both MN-major (bits 15, 16), bf16 in, fp32 accumulate
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(ncols >> 3) << 17) | (8u << 24);
-      for (int t = t0; t < t1; ++t) {
-        mbar_wait(full0 + 8 * stage, phase);
-        tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+    const bool leader = wg_elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    // M = 128, N = ncols, A and B both MN-major (bits 15, 16), bf16 in, fp32 accumulate
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(ncols >> 3) << 17) | (8u << 24);
+    const uint32_t smem_base = smem_u32(smem);
+    for (int t = t0; t < t1; ++t) {
+      mbar_wait(full0 + 8 * stage, phase);
+      tc_fence_after();
+      const uint32_t sa = smem_base + stage * stage_bytes;
+      if (leader) {
         for (int ti = 0; ti < ntap; ++ti) {
           const uint32_t sb = sa + (aboxes + ti * nboxes) * BOX_BYTES;
           for (int mt = 0; mt < mtiles; ++mt) {
@@ -189,15 +207,43 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
           }
         }
         umma_commit(empty0 + 8 * stage);
-        if (++stage == nstages) { stage = 0; phase ^= 1; }
       }
-      umma_commit(done);
+      __syncwarp();
+      if (++stage == nstages) { stage = 0; phase ^= 1; }
     }
+    if (leader) umma_commit(done);
+    __syncwarp();
   } else {
     const int lane_base = (warp & 3) * 32;
     mbar_wait(done, 0);
     tc_fence_after();
-    if (t1 > t0) {
+    if (p.ws) {
+      // two-stage reduction: this split's partial tile goes to the workspace with plain 16-byte stores
+      // (row = output channel: 128 contiguous bytes per thread and 32-column chunk); wgrad_reduce_kernel sums
+      // the splits.  Scalar atomics into the OIHW gradient (stride-9 addresses, 32 cache lines per warp
+      // instruction, every element hit by all splits) bound every 3x3 layer.
+      for (int ti = 0; ti < ntap; ++ti) {
+        for (int mt = 0; mt < mtiles; ++mt) {
+          const int n = n_off + mt * 128 + lane_base + lane;
+          const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + (ti * mtiles + mt) * ncols;
+          for (int c = 0; c < ncols / 32; ++c) {
+            uint32_t r[32];
+            if (t1 > t0) {
+              tmem_ld32(t_row + c * 32, r);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) r[j] = 0u;
+            }
+            if (n < p.Cout) {
+              const int cg = (from2 ? p.C1 : 0) + c_off + c * 32;
+              uint4* dst = reinterpret_cast<uint4*>(p.ws + (((long long)split * taps + tap0 + ti) * p.Cout + n) * p.Ctot + cg);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) dst[j] = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+            }
+          }
+        }
+      }
+    } else if (t1 > t0) {
       for (int ti = 0; ti < ntap; ++ti) {
         const int kh = (tap0 + ti) / p.KW, kw = (tap0 + ti) - kh * p.KW;
         for (int mt = 0; mt < mtiles; ++mt) {
@@ -235,6 +281,31 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
   }
+}
+
+// dw[n][c][tap] += sum over splits of ws[split][tap][n][c]; one thread per (tap, n, c) (blockIdx.y = tap): reads are
+// coalesced along c, eight independent loads in flight per thread
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ ws, int splits, int taps, int KW,
+                                                           int Cout, int Ctot, int Creal, float* __restrict__ dw,
+                                                           long long s_n, long long s_c, long long s_kh, long long s_kw) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long plane = (long long)Cout * Ctot;
+  if (i >= plane) return;
+  const int n = (int)(i / Ctot), c = (int)(i - (long long)n * Ctot);
+  if (c >= Creal) return;
+  const int tap = blockIdx.y;
+  const float* src = ws + tap * plane + i;
+  const long long step = (long long)taps * plane;
+  float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  int sp = 0;
+  for (; sp + 8 <= splits; sp += 8) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) a[u] += __ldg(src + (sp + u) * step);
+  }
+  for (; sp < splits; ++sp) a[0] += __ldg(src + sp * step);
+  const float acc = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+  const int kh = tap / KW, kw = tap - kh * KW;
+  dw[n * s_n + c * s_c + kh * s_kh + kw * s_kw] += acc;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -284,34 +355,16 @@ int make_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int ld
 
 }  // namespace
 
-extern "C" int hn_conv_wgrad_tc_supported(const HnConv* d) { return wg_ok(d) ? 1 : 0; }
-
-extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2, const void* dy, float* dw, int Creal,
-                                long long s_n, long long s_c, long long s_kh, long long s_kw, void* stream) {
-  HN_REQUIRE(wg_ok(d), "conv_wgrad_tc: geometry not supported by the tcgen05 path (use hn_conv2d_wgrad)");
-  HN_REQUIRE(x1 && dy && dw && (d->C2 == 0 || x2), "conv_wgrad_tc: null pointer");
-  PGeom g;
-  pix_geom(d->B, d->OH, d->OW, d->stride, &g);
-  CUtensorMap mdz, mx1, mx2;
-  PGeom g1 = g;
-  int rc = make_map(&mdz, dy, d->B, d->OH, d->OW, d->Cout, d->ldy, g1, 1);
-  if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(dz) = %d", rc);
-  rc = make_map(&mx1, x1, d->B, d->H, d->W, d->C1, d->ld1, g, d->stride);
-  if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(x1) = %d", rc);
-  if (d->C2) {
-    rc = make_map(&mx2, x2, d->B, d->H, d->W, d->C2, d->ld2, g, d->stride);
-    if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(x2) = %d", rc);
-  } else {
-    mx2 = mx1;
-  }
-  WgTc p;
-  p.Cout = d->Cout; p.C1 = d->C1; p.C2 = d->C2; p.Creal = Creal;
+// Work decomposition shared by the launch and the workspace query.
+static int wg_plan(const HnConv* d, const PGeom& g, WgTc* pp) {
+  WgTc& p = *pp;
+  p.Cout = d->Cout; p.C1 = d->C1; p.C2 = d->C2;
   p.KH = d->KH; p.KW = d->KW; p.pad = d->pad; p.dil = d->dil; p.es = d->stride;
   p.BW = g.BW; p.BH = g.BH; p.BB = g.BB; p.tiles_w = d->OW / g.BW; p.tiles_h = d->OH / g.BH;
   p.ptiles = (int)((long long)d->B * d->OH * d->OW / PK);
   p.mblocks = (d->Cout + 255) / 256;
   p.ct1 = (d->C1 + 255) / 256; p.ct2 = (d->C2 + 255) / 256;
-  p.s_n = s_n; p.s_c = s_c; p.s_kh = s_kh; p.s_kw = s_kw; p.dw = dw;
+  p.Ctot = d->C1 + d->C2;
   // taps per work item: as many (tap, m-tile) accumulators of nc_max columns as the 512 TMEM columns hold,
   // at most 7 boxes of x per stage, balanced over the groups
   const int taps = d->KH * d->KW;
@@ -344,6 +397,47 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
     int st = (192 * 1024) / ((ab + nb) * BOX_BYTES);
     p.stages = st > WG_STAGES ? WG_STAGES : (st < 2 ? 2 : st);
   }
+  return jobs;
+}
+
+// fp32 elements of workspace that turn the flush into stores + one reduce pass (0: the 1x1 vector-reduction path)
+extern "C" long long hn_conv_wgrad_tc_workspace(const HnConv* d, long long s_c) {
+  if (!wg_ok(d) || s_c == 1) return 0;
+  PGeom g;
+  pix_geom(d->B, d->OH, d->OW, d->stride, &g);
+  WgTc p;
+  wg_plan(d, g, &p);
+  return (long long)p.splits * d->KH * d->KW * p.Cout * p.Ctot;
+}
+
+extern "C" int hn_conv_wgrad_tc_supported(const HnConv* d) { return wg_ok(d) ? 1 : 0; }
+
+extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2, const void* dy, float* dw, int Creal,
+                                long long s_n, long long s_c, long long s_kh, long long s_kw, float* workspace,
+                                long long workspace_floats, void* stream) {
+  HN_REQUIRE(wg_ok(d), "conv_wgrad_tc: geometry not supported by the tcgen05 path (use hn_conv2d_wgrad)");
+  HN_REQUIRE(x1 && dy && dw && (d->C2 == 0 || x2), "conv_wgrad_tc: null pointer");
+  PGeom g;
+  pix_geom(d->B, d->OH, d->OW, d->stride, &g);
+  CUtensorMap mdz, mx1, mx2;
+  PGeom g1 = g;
+  int rc = make_map(&mdz, dy, d->B, d->OH, d->OW, d->Cout, d->ldy, g1, 1);
+  if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(dz) = %d", rc);
+  rc = make_map(&mx1, x1, d->B, d->H, d->W, d->C1, d->ld1, g, d->stride);
+  if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(x1) = %d", rc);
+  if (d->C2) {
+    rc = make_map(&mx2, x2, d->B, d->H, d->W, d->C2, d->ld2, g, d->stride);
+    if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(x2) = %d", rc);
+  } else {
+    mx2 = mx1;
+  }
+  WgTc p;
+  const int jobs = wg_plan(d, g, &p);
+  p.Creal = Creal;
+  p.s_n = s_n; p.s_c = s_c; p.s_kh = s_kh; p.s_kw = s_kw; p.dw = dw;
+  const int taps = d->KH * d->KW;
+  const long long need = (long long)p.splits * taps * p.Cout * p.Ctot;
+  p.ws = (s_c != 1 && workspace && workspace_floats >= need) ? workspace : nullptr;
   const int SMEM = 192 * 1024 + 1024;
   static bool configured = false;
   if (!configured) {
@@ -353,5 +447,11 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
   }
   wgrad_tc_kernel<<<jobs * p.splits, WG_THREADS, SMEM, (cudaStream_t)stream>>>(mdz, mx1, mx2, p);
   HN_CHECK_LAUNCH("wgrad_tc_kernel");
+  if (p.ws) {
+    const long long nthr = (long long)p.Cout * p.Ctot;
+    wgrad_reduce_kernel<<<dim3((unsigned)((nthr + 255) / 256), taps), 256, 0, (cudaStream_t)stream>>>(p.ws, p.splits, taps, d->KW, p.Cout, p.Ctot, Creal,
+                                                                                     dw, s_n, s_c, s_kh, s_kw);
+    HN_CHECK_LAUNCH("wgrad_reduce_kernel");
+  }
   return HN_OK;
 }

@@ -322,6 +322,11 @@ def _wgrad_raw(x1, x2, dz, dw, *, Creal, OH, OW, Cout, KH, KW, stride, pad, dil,
         name = "hn_conv_wgrad_tc"
     else:
         name = "hn_conv2d_wgrad"
+    if name == "hn_conv_wgrad_tc":
+        nws = lib.hn_conv_wgrad_tc_workspace(d, strides[1])       # partial sums of the split-K items (3x3 weights)
+        ws = torch.empty(nws, dtype=torch.float32, device=dz.device) if nws > 0 else None
+        call(name, d, x1.data_ptr(), _ptr(x2), dz.data_ptr(), dw.data_ptr(), Creal, *strides, _ptr(ws), nws, _stream())
+        return
     call(name, d, x1.data_ptr(), _ptr(x2), dz.data_ptr(), dw.data_ptr(), Creal, *strides, _stream())
 
 
