@@ -18,6 +18,8 @@ GEOMS = [
     ("ae_3x3_192_64_256", 16, 256, 256, 192, 0, 64, 3, 1, 1, 0, 1),
     ("ae_3x3_64_192_256", 16, 256, 256, 64, 0, 192, 3, 1, 1, 0, 0),
     ("ae_k2s2_192_384", 16, 256, 256, 192, 0, 384, 2, 2, 1, 0, 0),
+    ("ae_3x3_8_64_256", 16, 256, 256, 8, 0, 64, 3, 1, 1, 0, 0),
+    ("ae_3x3_64_8_256", 16, 256, 256, 64, 0, 8, 3, 1, 1, 0, 1),
     ("un_3x3_32_32", 32, 256, 256, 32, 0, 32, 3, 1, 1, 0, 1),
     ("un_3x3_32+32_32", 32, 256, 256, 32, 32, 32, 3, 1, 1, 0, 1),
     ("un_3x3_64_64", 32, 128, 128, 64, 0, 64, 3, 1, 1, 0, 1),

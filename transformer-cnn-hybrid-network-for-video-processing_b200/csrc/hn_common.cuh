@@ -91,10 +91,16 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
   return cdf + x * pdf;
 }
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+// Epilogue activation with a RUNTIME selector.  none/ReLU are branch-free (FMNMX + FSEL); GELU and
+// sigmoid sit behind a warp-uniform branch to an out-of-line call.  Inlining erff at each of the 64-128 unrolled
+// epilogue sites made conv_sc_kernel<8> instruction-fetch bound (ncu: 44 % of samples on BSYNC with stall_no_inst,
+// profiles/r1_end_ncu_full_conv_sc_8_64.txt) and put an indirect branch into every conv_tc epilogue chunk.
+static __device__ __noinline__ float apply_act_slow(float v, int act) {
+  return act == HN_ACT_GELU ? gelu_f(v) : sigmoid_f(v);
+}
 __device__ __forceinline__ float apply_act(float v, int act) {
-  if (act == HN_ACT_RELU) return fmaxf(v, 0.f);
-  if (act == HN_ACT_GELU) return gelu_f(v);
-  if (act == HN_ACT_SIGMOID) return sigmoid_f(v);
+  v = act == HN_ACT_RELU ? fmaxf(v, 0.f) : v;          // FMNMX + FSEL, NaN passes through when there is no activation
+  if (act > HN_ACT_RELU) v = apply_act_slow(v, act);
   return v;
 }
 
