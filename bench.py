@@ -342,7 +342,7 @@ def main():
             return infer_step(xd, yd)
         arena.zero_grad()
         ops.begin_step(dev, zero_cap)           # all zero-initialised fp32 scratch of the step: one memset
-        ops.invalidate_packed()                 # weights change every step in training: pay for the repack
+        ops.repack_all()                        # weights change every step in training: pay for the repack (one launch)
         out = model(xd)
         loss = loss_fn(kind, out, xd, yd)
         loss.backward()

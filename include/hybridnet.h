@@ -79,6 +79,11 @@ int hn_conv_npad(int Cout);                      /* packed row count            
 int hn_pack_weight(const float* src, void* dst, int N, int Creal, int Cpad, int KH, int KW,
                    long long nmod, long long s_nhi, long long s_n, long long s_c,
                    long long s_kh, long long s_kw, void* stream);
+/* Every weight pack of a model in one launch.  jobs = DEVICE array of njobs records of 16 x int64:
+ *   { src, dst, N, Npad, Creal, Cpad, KH, KW, Kpad, nmod, s_nhi, s_n, s_c, s_kh, s_kw, s2k }
+ * = the arguments of hn_pack_weight (Npad = hn_conv_npad(N), Kpad = hn_conv_kpad(KH,KW,Cpad)); s2k != 0 selects
+ * the hn_pack_weight_s2dgrad layout instead (N = Cout, Creal = Cin, s2k = K, Npad/Kpad as that call defines). */
+int hn_pack_weight_multi(const void* jobs, int njobs, long long max_elems /* largest Npad*Kpad */, void* stream);
 /* Packed B operand for the input gradient of a stride-2 conv (k in {1,3}, pad k/2; the reference's
  * Bottleneck conv2 / downsample, pyc:AE_32K:L20-53) run as one stride-1 tcgen05 GEMM over dz with a 2x2
  * (k3) or 1x1 (k1) window and a pixel-shuffle store: rows (py,px,ci), columns (dh,dw,co).

@@ -349,7 +349,7 @@ def test_captured_step_matches_eager_and_redraws_dropout():
     def step(xd, yd):
         arena.zero_grad()
         ops.begin_step(dev, cap_floats)         # zero pool: one memset for every fp32 accumulator of the step
-        ops.invalidate_packed()
+        ops.repack_all()                        # every bf16 weight copy refreshed by one launch
         out = m(xd)
         p, t = out[:, 0].reshape(-1), yd[:, 0].reshape(-1)
         loss = 1.0 - (2.0 * torch.dot(p, t) + 1.0) / (p.sum() + t.sum() + 1.0)

@@ -124,6 +124,53 @@ def test_stride2_input_gradient_runs_on_tcgen05(ops, cin, cout, k, H, tc):
     assert rel_l2(x.grad, xr) < BWD_TOL
 
 
+def test_repack_all_refreshes_every_packed_weight(ops):
+    """ops.repack_all(): one hn_pack_weight_multi launch re-derives all bf16 weight copies (forward, flipped-tap
+    input-gradient, stride-2 input-gradient and transposed-conv layouts) after an in-place weight update."""
+    import contextlib
+    from hybridnet import _lib
+    ops.invalidate_packed()
+    x = _rand(2, 64, 16, 16, seed=21).requires_grad_(True)
+    w3 = _rand(64, 64, 3, 3, seed=22, scale=0.05).requires_grad_(True)       # stride 1: fwd + dgradf
+    w2 = _rand(128, 64, 3, 3, seed=23, scale=0.05).requires_grad_(True)      # stride 2: fwd + s2dgrad
+    wt = _rand(128, 32, 2, 2, seed=24, scale=0.05).requires_grad_(True)      # ConvTranspose k2s2: tfwd + tdgrad
+
+    def run():
+        for t in (x, w3, w2, wt):
+            t.grad = None
+        h = ops.conv2d(ops.to_nhwc(x), w3, None)
+        h = ops.conv2d(h, w2, None, stride=2, pad=1)
+        y = ops.to_nchw(ops.conv2d(h, wt, None, stride=2, pad=0, transposed=True), 32)
+        y.backward(torch.ones_like(y))
+        return y.detach().clone(), x.grad.clone()
+
+    y1, g1 = run()
+    with torch.no_grad():
+        for t in (w3, w2, wt):
+            t.mul_(2.0)
+    names = []
+
+    @contextlib.contextmanager
+    def rec(name, args):
+        names.append(name)
+        yield
+
+    _lib.set_profiler(rec)
+    try:
+        n = ops.repack_all()
+        y2, g2 = run()
+    finally:
+        _lib.set_profiler(None)
+    assert n == 6, n
+    assert names.count("hn_pack_weight_multi") == 1 and not any(k.startswith("hn_pack_weight") and k != "hn_pack_weight_multi" for k in names), names
+    assert rel_l2(y2, 8.0 * y1) < 1e-6 and rel_l2(g2, 8.0 * g1) < 1e-6      # powers of two: exact in bf16
+    with torch.no_grad():
+        w3.mul_(0.5)
+    y3, _ = run()                      # without repack_all the version check makes the layer repack itself
+    assert rel_l2(y3, 4.0 * y1) < 1e-6
+    ops.invalidate_packed()
+
+
 def test_conv_virtual_concat_upsample_residual(ops):
     """cat([a,b]) folded into the K loop; nearest-x2 upsample folded into the gather; residual epilogue."""
     B, H = 2, 16

@@ -36,6 +36,7 @@ SIGNATURES = {
     "hn_conv_npad": [_I],
     "hn_pack_weight": [_FP, _P, _I, _I, _I, _I, _I, _L, _L, _L, _L, _L, _L, _P],
     "hn_pack_weight_s2dgrad": [_FP, _P, _I, _I, _I, _P],
+    "hn_pack_weight_multi": [_P, _I, _L, _P],
     "hn_conv2d_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _P, _FP, _FP, _P],
     "hn_conv2d_wgrad": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _P],
     "hn_act_bwd": [_P, _P, _P, _L, _I, _I, _I, _I, _I, _FP, _P],

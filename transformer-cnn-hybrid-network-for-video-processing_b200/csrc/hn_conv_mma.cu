@@ -394,6 +394,66 @@ extern "C" int hn_pack_weight_s2dgrad(const float* src, void* dst, int Cout, int
   return HN_OK;
 }
 
+// ---- all weight packs of a model in ONE launch ------------------------------------------------------------------
+// jobs: device array of HnPackJob (16 x i64 each, see include/hybridnet.h); blockIdx.y = job.  A training step
+// repacks every conv weight after the optimizer update: 45-214 launches of 2-5 us each otherwise.
+struct PackJob {
+  long long src, dst, N, Npad, Creal, Cpad, KH, KW, Kpad, nmod, s_nhi, s_n, s_c, s_kh, s_kw, s2k;
+};
+__global__ void __launch_bounds__(256) pack_weight_multi_kernel(const PackJob* __restrict__ jobs) {
+  const PackJob j = jobs[blockIdx.y];
+  const float* __restrict__ src = reinterpret_cast<const float*>(j.src);
+  bf16* __restrict__ dst = reinterpret_cast<bf16*>(j.dst);
+  const long long total = j.Npad * j.Kpad;
+  const int Kpad = (int)j.Kpad;
+  if (j.s2k) {                       // stride-2 input-gradient layout (pack_weight_s2dgrad_kernel): N = Cout, Creal = Cin
+    const int Cout = (int)j.N, Cin = (int)j.Creal, K = (int)j.s2k, win = K == 3 ? 2 : 1;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+      const int n = (int)(i / Kpad), k = (int)(i - (long long)n * Kpad);
+      float v = 0.f;
+      if (n < 4 * Cin && k < win * win * Cout) {
+        const int par = n / Cin, ci = n - par * Cin, py = par >> 1, px = par & 1;
+        const int tap = k / Cout, co = k - tap * Cout, dh = tap / win, dw = tap - dh * win;
+        int kh, kw;
+        if (K == 3) {
+          kh = py == 0 ? (dh == 0 ? 1 : -1) : (dh == 0 ? 2 : 0);
+          kw = px == 0 ? (dw == 0 ? 1 : -1) : (dw == 0 ? 2 : 0);
+        } else {
+          kh = py == 0 ? 0 : -1;
+          kw = px == 0 ? 0 : -1;
+        }
+        if (kh >= 0 && kw >= 0) v = src[(((long long)co * Cin + ci) * K + kh) * K + kw];
+      }
+      dst[i] = __float2bfloat16(v);
+    }
+    return;
+  }
+  const int N = (int)j.N, Creal = (int)j.Creal, Cpad = (int)j.Cpad, KH = (int)j.KH, KW = (int)j.KW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / Kpad), k = (int)(i - (long long)n * Kpad);
+    const int tap = k / Cpad, c = k - tap * Cpad;
+    float v = 0.f;
+    if (n < N && tap < KH * KW && c < Creal) {
+      const int kh = tap / KW, kw = tap - kh * KW;
+      v = src[(n / j.nmod) * j.s_nhi + (n % j.nmod) * j.s_n + c * j.s_c + kh * j.s_kh + kw * j.s_kw];
+    }
+    dst[i] = __float2bfloat16(v);
+  }
+}
+
+extern "C" int hn_pack_weight_multi(const void* jobs, int njobs, long long max_elems, void* stream) {
+  HN_REQUIRE(jobs && njobs > 0 && njobs <= 65535 && max_elems > 0, "pack_weight_multi: bad args");
+  // blocks per job sized for the LARGEST job (2 elements per thread, at most four waves in total); the blocks a
+  // small job does not need fall straight through their grid-stride loop
+  long long bx = (max_elems + 511) / 512;
+  const long long cap = (148LL * 8 * 4 + njobs - 1) / njobs;
+  if (bx > cap) bx = cap;
+  if (bx < 8) bx = 8;
+  pack_weight_multi_kernel<<<dim3((unsigned)bx, njobs), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const PackJob*>(jobs));
+  HN_CHECK_LAUNCH("pack_weight_multi_kernel");
+  return HN_OK;
+}
+
 extern "C" int hn_pack_weight(const float* src, void* dst, int N, int Creal, int Cpad, int KH, int KW,
                               long long nmod, long long s_nhi, long long s_n, long long s_c,
                               long long s_kh, long long s_kw, void* stream) {

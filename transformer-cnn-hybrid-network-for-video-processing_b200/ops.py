@@ -211,6 +211,7 @@ def _packed(w, kind, Cpad):
         buf = torch.empty((lib.hn_conv_npad(4 * d1), Kpad), dtype=torch.bfloat16, device=w.device)
         call("hn_pack_weight_s2dgrad", src.data_ptr(), buf.data_ptr(), d0, d1, KH, _stream())
         ent[key] = (buf, Kpad)
+        ent.setdefault("jobs", {})[key] = [src.data_ptr(), buf.data_ptr(), d0, buf.shape[0], d1, 0, 0, 0, Kpad, 1, 0, 0, 0, 0, 0, KH]
         return ent[key]
     assert kind != "dgradf" or src.is_contiguous()
     big = 1 << 40
@@ -238,7 +239,40 @@ def _packed(w, kind, Cpad):
     buf = torch.empty((Npad, Kpad), dtype=torch.bfloat16, device=w.device)
     call("hn_pack_weight", src.data_ptr(), buf.data_ptr(), N, Creal, Cpad, kh, kw, *args, _stream())
     ent[key] = (buf, Kpad)
+    ent.setdefault("jobs", {})[key] = [src.data_ptr(), buf.data_ptr(), N, Npad, Creal, Cpad, kh, kw, Kpad, *args, 0]
     return ent[key]
+
+
+_repack_table = {"sig": None, "dev": None, "n": 0, "max": 1}
+
+
+def repack_all():
+    """Refresh EVERY packed bf16 weight copy made so far with one launch (``hn_pack_weight_multi``) and mark
+    them current -- what a training loop calls after the optimizer step instead of ``invalidate_packed()`` (which
+    makes each layer repack itself: one tiny launch per weight).  Packs created later (first use of a layer)
+    are picked up by the next call.  Returns the number of packs refreshed."""
+    jobs, dev = [], None
+    for ent in _pack_cache.values():
+        owner = ent["ref"]()
+        if owner is None or "jobs" not in ent:
+            continue
+        if ent["ver"][1] != owner.data_ptr():          # storage moved (.to()): let the lazy path rebuild it
+            continue
+        ent["ver"] = (owner._version, owner.data_ptr())
+        dev = owner.device
+        jobs.extend(ent["jobs"].values())
+    if not jobs:
+        return 0
+    sig = (len(jobs), hash(tuple(j[0] for j in jobs)), hash(tuple(j[1] for j in jobs)))
+    if _repack_table["sig"] != sig:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("hybridnet.ops.repack_all: the set of packed weights changed inside a graph capture; "
+                               "run one eager step first")
+        _repack_table["dev"] = torch.tensor(jobs, dtype=torch.int64, device=dev)
+        _repack_table["sig"], _repack_table["n"] = sig, len(jobs)
+        _repack_table["max"] = max(j[3] * j[8] for j in jobs)
+    call("hn_pack_weight_multi", _repack_table["dev"].data_ptr(), _repack_table["n"], _repack_table["max"], _stream())
+    return len(jobs)
 
 
 def invalidate_packed():

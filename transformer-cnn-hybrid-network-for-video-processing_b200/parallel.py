@@ -162,8 +162,8 @@ class CapturedStep:
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            for _ in range(max(1, warmup)):
-                body()
+            for _ in range(max(2, warmup)):      # >= 2: state built lazily by the first step (packed-weight table of
+                body()                           # ops.repack_all, kernel attributes) must exist before capture
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
