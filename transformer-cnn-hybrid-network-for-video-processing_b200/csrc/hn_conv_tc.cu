@@ -146,6 +146,36 @@ __device__ __forceinline__ float colsum32(float* v, int lane) {
   return v[0];
 }
 
+// Column sums and sums of squares of a 32(row = lane) x 32(col) block of bf16-rounded values through a per-warp
+// shared-memory transpose: every lane writes its row as 4 x 16 bytes (chunks XOR-swizzled by (row >> 1) & 3:
+// conflict-free), then lane j walks column j (LDS + PRMT + FADD + FFMA per row).  ~150 instructions for both
+// statistics; the register butterfly (colsum32 twice: 62 SHFL + 124 FSEL + 62 FADD) was ~46 % of all
+// instructions of the epilogue-bound 1x1 layers (profiles/r1_end_ncu_full_conv_tc_1x1_64_256.txt).
+constexpr int TR_BYTES = 32 * 64;
+__device__ __forceinline__ void colstats32(const float* v, uint8_t* tr, int lane, float& s_out, float& q_out) {
+  uint32_t pk[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+  const int sw = (lane >> 1) & 3;
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+    *reinterpret_cast<uint4*>(tr + lane * 64 + ((c ^ sw) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+  __syncwarp();
+  const int cw = lane >> 3, wofs = ((lane & 7) >> 1) * 4;
+  const uint32_t sel = (lane & 1) ? 0x3244u : 0x1044u;      // bf16 half of the word -> fp32 bits
+  float s = 0.f, q = 0.f;
+#pragma unroll
+  for (int r = 0; r < 32; ++r) {
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(tr + r * 64 + ((cw ^ ((r >> 1) & 3)) << 4) + wofs);
+    const float f = __uint_as_float(__byte_perm(w, 0u, sel));
+    s += f;
+    q = fmaf(f, f, q);
+  }
+  __syncwarp();
+  s_out = s;
+  q_out = q;
+}
+
 template <int BN, int BKC>
 __global__ void __launch_bounds__(NTHREADS_TC, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
@@ -165,6 +195,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   // BatchNorm sum / sum-of-squares are accumulated per CTA here and flushed with ONE global atomic per
   // channel per CTA at the end (per-tile global atomics serialise on the same few addresses in L2)
   __shared__ float s_stat[2][STAT_MAX];
+  __shared__ __align__(16) uint8_t s_tr[8][TR_BYTES];       // per epilogue warp: transpose scratch of colstats32
   if (p.ssum) {
     for (int i = threadIdx.x; i < 2 * STAT_MAX; i += NTHREADS_TC) (&s_stat[0][0])[i] = 0.f;
   }
@@ -291,13 +322,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __ldg(p.bias + ch0 + j);
         }
         if (p.ssum) {
-          float t[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) t[j] = bf16_round(v[j]);
-          float s = colsum32(t, lane);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) { float q = bf16_round(v[j]); t[j] = q * q; }
-          float q = colsum32(t, lane);
+          float s, q;
+          colstats32(v, s_tr[warp - 2], lane, s, q);
           atomicAdd(&s_stat[0][ch0 + lane], s);
           atomicAdd(&s_stat[1][ch0 + lane], q);
         }
@@ -363,6 +389,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
   __shared__ __align__(8) uint64_t bars[2 * 8 + 5];
   __shared__ uint32_t tmem_base_slot;
   __shared__ float s_stat[2][HALO_STAT_MAX];
+  __shared__ __align__(16) uint8_t s_tr[8][TR_BYTES];
   if (p.ssum) {
     for (int i = threadIdx.x; i < 2 * HALO_STAT_MAX; i += NTHREADS_TC) (&s_stat[0][0])[i] = 0.f;
   }
@@ -479,13 +506,8 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(p.bias + ch0 + j) : 0.f);
         if (p.ssum) {
-          float t[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) t[j] = bf16_round(v[j]);
-          float s = colsum32(t, lane);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) { float q = bf16_round(v[j]); t[j] = q * q; }
-          float q = colsum32(t, lane);
+          float s, q;
+          colstats32(v, s_tr[warp - 2], lane, s, q);
           atomicAdd(&s_stat[0][ch0 + lane], s);
           atomicAdd(&s_stat[1][ch0 + lane], q);
         }
