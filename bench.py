@@ -44,40 +44,51 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe).  One streaming
+    `nvidia-smi -lms 20` process is started well before the timed region (its start-up costs ~100 ms); rows are
+    time-stamped on arrival and the summary uses the rows that fell inside the region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.stop = index, [], False
+        self.index, self.rows, self.t0, self.t1, self.proc = index, [], None, None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                          str(index), "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                                         text=True, bufsize=1)
+        except Exception:
+            self.proc = None
         self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
 
     def _run(self):
-        while not self.stop:
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
-                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
-            except Exception:
-                pass
-            time.sleep(0.05)
+        if self.proc is None:
+            return
+        for line in self.proc.stdout:
+            cells = [c.strip() for c in line.strip().split(",")]
+            if len(cells) >= 6:
+                self.rows.append((time.perf_counter(), cells))
 
     def __enter__(self):
-        self.t.start()
+        self.t0 = time.perf_counter()
         return self
 
     def __exit__(self, *a):
-        self.stop = True
+        self.t1 = time.perf_counter()
+        time.sleep(0.03)                      # let the last in-region sample arrive
+        if self.proc is not None:
+            self.proc.terminate()
         self.t.join(timeout=3)
 
     def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
+        inside = [c for ts, c in self.rows if self.t0 is not None and self.t0 <= ts <= (self.t1 or ts) + 0.03]
+        rows = inside or [c for _, c in self.rows[-3:]]
+        sm = sorted(int(r[0]) for r in rows if r[0].isdigit())
+        mx = [int(r[1]) for r in rows if r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        reasons = sorted({n for r in rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(inside)}
 
 
 def make_batch(B, seed, device, pinned=False):
@@ -354,6 +365,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    clocks = ClockSampler(local)                # streaming nvidia-smi, started ahead of the timed region
     for _ in range(args.warmup):
         step(x, y)
     barrier()
@@ -371,7 +383,7 @@ def main():
     # ---- timed region 1: inputs resident in HBM ------------------------------------------------
     _lib.stats["launches"] = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
+    with clocks:
         barrier()
         e0.record()
         for _ in range(args.steps):
