@@ -213,6 +213,22 @@ def test_eval_mode_inference_matches_oracle():
     with torch.no_grad():
         out = m(x.cuda()).cpu()
     assert max_abs(out, ref) <= OUT_ABS and rel_l2(out, ref) <= OUT_REL
+    # the inference path folds eval-mode BatchNorm into the conv weights (ops.FOLD_EVAL_BN): it must agree with the
+    # unfolded kernels (bn_apply on running statistics) to bf16 rounding, and follow a changed running statistic
+    from hybridnet import ops
+    ops.FOLD_EVAL_BN = False
+    try:
+        with torch.no_grad():
+            plain = m(x.cuda()).cpu()
+    finally:
+        ops.FOLD_EVAL_BN = True
+    assert max_abs(plain, ref) <= OUT_ABS and rel_l2(out, plain) <= OUT_REL
+    with torch.no_grad():
+        m[1].bn5.running_var.mul_(4.0)
+        sd2 = {k: v.cpu() for k, v in m.state_dict().items()}
+        out2 = m(x.cuda()).cpu()
+    ref2 = nets.FORWARDS[name](sd2, x, nets.Ctx(training=False))
+    assert max_abs(out2, ref2) <= OUT_ABS and rel_l2(out2, ref2) <= OUT_REL and max_abs(out2, out) > 1e-4
 
 
 def test_linearity_of_weight_gradient_at_full_batch():

@@ -701,11 +701,37 @@ class _ConvStatsFn(torch.autograd.Function):
         return (dx1 if need[0] else None, dx2 if need[1] else None, dw, dbias, None, None, None, None, None)
 
 
+FOLD_EVAL_BN = os.environ.get("HN_DISABLE_BN_FOLD", "0") != "1"
+_fold_cache = {}          # id(bn) -> (signature, folded weight, folded bias); dropped with the module
+
+
+def _folded_eval_bn(weight, bias, bn, transposed):
+    ts = (weight, bias, bn.weight, bn.bias, bn.running_mean, bn.running_var)
+    sig = tuple((t.data_ptr(), t._version) if t is not None else None for t in ts) + (transposed, bn.eps)
+    ent = _fold_cache.get(id(bn))
+    if ent is not None and ent[0] == sig and ent[3]() is bn:
+        return ent[1], ent[2]
+    with torch.no_grad():
+        scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps)
+        shift = bn.bias.float() - bn.running_mean.float() * scale
+        wf = (weight.float() * (scale.view(1, -1, 1, 1) if transposed else scale.view(-1, 1, 1, 1))).contiguous()
+        bf = (shift if bias is None else bias.float() * scale + shift).contiguous()
+    key = id(bn)
+    _fold_cache[key] = (sig, wf, bf, weakref.ref(bn, lambda _r, key=key: _fold_cache.pop(key, None)))
+    return wf, bf
+
+
 def conv_bn_act(x, weight, bias, bn, *, x2=None, res=None, stride=1, pad=1, dil=1, ups=0, act="relu",
                 transposed=False):
     """Conv2d/ConvTranspose2d -> BatchNorm2d -> activation (UNet.py:54-66; pyc:AE_32K).  In training
     the batch statistics ride the conv epilogue; ``bn`` is the BatchNorm2d module (params + buffers)."""
     training = bn.training or (bn.running_mean is None)
+    if not training and res is None and not torch.is_grad_enabled() and FOLD_EVAL_BN:
+        # inference: eval-mode BatchNorm is a per-channel affine map of the conv output -- fold it into the conv's
+        # weights and bias (fp32, cached until a parameter / running statistic changes) and let the conv epilogue
+        # apply the activation: no BN pass at all (Bottleneck's bn3 + residual keeps the bn_apply path)
+        wf, bf = _folded_eval_bn(weight, bias, bn, transposed)
+        return conv2d(x, wf, bf, x2=x2, stride=stride, pad=pad, dil=dil, ups=ups, act=act, transposed=transposed)
     if training:
         z, s0, s1 = _ConvStatsFn.apply(x, x2, weight, bias, stride, pad, dil, ups, transposed)
         stats = (s0, s1)
