@@ -32,6 +32,8 @@ GEOMS = [
     ("fct_1x1_8_8", 32, 128, 128, 8, 0, 8, 1, 1, 1, 0, 0),
     ("fct_3x3_32_32", 32, 64, 64, 32, 0, 32, 3, 1, 1, 0, 0),
     ("fct_3x3_8_1", 32, 256, 256, 8, 0, 1, 3, 1, 1, 0, 0),
+    ("fct_s32_3x3_32_32", 32, 32, 32, 32, 0, 32, 3, 1, 1, 0, 0),
+    ("fct_s16_3x3_64_64", 32, 16, 16, 64, 0, 64, 3, 1, 1, 0, 0),
 ]
 
 

@@ -186,7 +186,7 @@ int launch_ws(const WsP& p, int smem, cudaStream_t st) {
   }
   int per_sm = occ[bucket] > 3 ? 3 : occ[bucket];          // more CTAs only multiply the final atomics
   int grid = 148 * per_sm;
-  if (grid > (p.tiles + 3) / 4) grid = (p.tiles + 3) / 4;   // >= 4 tiles per CTA: the flush costs Cout*K atomics per CTA
+  if (grid > (p.tiles + 1) / 2) grid = (p.tiles + 1) / 2;   // >= 2 tiles per CTA (measured: 4 starves the small FCT levels, 1 doubles the flush atomics)
   wgrad_sc_kernel<MTN, CPW><<<grid, WS_THREADS, smem, st>>>(p);
   HN_CHECK_LAUNCH("wgrad_sc_kernel");
   return HN_OK;
