@@ -442,3 +442,59 @@ def test_captured_step_matches_eager_and_redraws_dropout():
     losses = {round(float(fc()), 7) for _ in range(4)}
     assert len(losses) == 4, losses
     ops.end_zero_pool()
+
+
+@pytest.mark.gpu
+def test_captured_step_prefetch_and_download_pipeline():
+    """CapturedStep.prefetch / download: batches staged on the copy stream while the previous replay runs,
+    and results copied back on the download stream, give exactly what the synchronous call gives for the
+    same batches, in order (eval-mode BN: the forward is deterministic)."""
+    import hybridnet
+    from hybridnet import ops, parallel
+    torch.manual_seed(3)
+    dev = torch.device("cuda")
+    m = hybridnet.UNet().to(dev).eval()
+    y = torch.zeros(2, 1, 64, 64, device=dev)
+    batches = [torch.rand(2, 3, 64, 64).pin_memory() for _ in range(5)]
+    yh = torch.zeros(2, 1, 64, 64).pin_memory()
+
+    def fwd(xd, yd):
+        with torch.no_grad():
+            return m(xd)
+
+    cap = parallel.CapturedStep(fwd, batches[0].to(dev), y, warmup=1)
+    want = [cap(b, yh).clone().cpu() for b in batches]           # synchronous: copy, replay, read back
+    assert float((want[0] - want[1]).abs().max()) > 1e-4
+
+    got, handles = [], []
+    cap.prefetch(batches[0], yh)
+    with pytest.raises(RuntimeError):
+        cap.prefetch(batches[1], yh)                             # one batch in flight at a time
+    for i in range(len(batches)):
+        cap()
+        if i + 1 < len(batches):
+            cap.prefetch(batches[i + 1])                         # y optional
+        h = cap.download()
+        if handles:
+            got.append(handles[-1].wait().clone())               # pinned buffers are reused two calls later
+        handles.append(h)
+    got.append(handles[-1].wait().clone())
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+
+    # losses through the training-loop form: item() per step with the next batch already in flight
+    def lstep(xd, yd):
+        with torch.no_grad():
+            return m(xd).mean()
+
+    capl = parallel.CapturedStep(lstep, batches[0].to(dev), y, warmup=1)
+    ref = [float(capl(b, yh)) for b in batches]
+    capl.prefetch(batches[0], yh)
+    out = []
+    for i in range(len(batches)):
+        loss = capl()
+        if i + 1 < len(batches):
+            capl.prefetch(batches[i + 1], yh)
+        out.append(float(loss.item()))
+    assert out == ref

@@ -177,8 +177,81 @@ class CapturedStep:
             self.x.copy_(x, non_blocking=True)
         if y is not None:
             self.y.copy_(y, non_blocking=True)
+        if x is None and y is None and self._pending is not None:
+            k, self._pending = self._pending, None
+            cur = torch.cuda.current_stream()
+            cur.wait_event(self._ready[k])            # the prefetched batch has landed in its staging pair
+            self.x.copy_(self._stage[k][0], non_blocking=True)   # device-to-device, ~10 us for 16 frames
+            if self._staged_y[k]:
+                self.y.copy_(self._stage[k][1], non_blocking=True)
+            self._freed[k].record(cur)
         self.graph.replay()
         return self.loss
+
+    # ---- copy/compute overlap --------------------------------------------------------------------------
+    # The graph reads static buffers, so a batch cannot be copied into them while the previous replay is
+    # still running.  prefetch() lands the NEXT batch in one of two staging pairs on a copy stream while
+    # the current step computes; the following call moves it into the static buffers device-to-device.
+    # download() does the same for results that go back to the host whole (inference masks).
+    _pending = None
+    _copy = None
+    _down = None
+
+    def prefetch(self, x, y=None):
+        """Start the host-to-device copy of the next batch (pinned host tensors) on the copy stream.
+        The next ``step()`` call without arguments consumes it."""
+        if self._copy is None:
+            dev = self.x.device
+            self._copy = torch.cuda.Stream(device=dev)
+            self._stage = [(torch.empty_like(self.x), torch.empty_like(self.y)) for _ in range(2)]
+            self._ready = [torch.cuda.Event() for _ in range(2)]
+            self._freed = [torch.cuda.Event() for _ in range(2)]
+            self._staged_y = [False, False]
+            self._k = 0
+        if self._pending is not None:
+            raise RuntimeError("CapturedStep.prefetch: the previously prefetched batch has not been consumed")
+        k = self._k
+        self._k ^= 1
+        with torch.cuda.stream(self._copy):
+            self._copy.wait_event(self._freed[k])     # the step that last read this pair has drained it
+            self._stage[k][0].copy_(x, non_blocking=True)
+            if y is not None:
+                self._stage[k][1].copy_(y, non_blocking=True)
+            self._ready[k].record(self._copy)
+        self._staged_y[k] = y is not None
+        self._pending = k
+
+    class _Download:
+        def __init__(self, host, done):
+            self.host, self.done = host, done
+
+        def wait(self):
+            """Block until the result is in pinned host memory; returns that tensor (reused two calls later)."""
+            self.done.synchronize()
+            return self.host
+
+    def download(self):
+        """Queue the device-to-host copy of the last replay's result on the download stream and return a
+        handle; ``handle.wait()`` gives the pinned host tensor.  The next replay may start meanwhile."""
+        if self._down is None:
+            dev = self.x.device
+            self._down = torch.cuda.Stream(device=dev)
+            self._out_stage = [torch.empty_like(self.loss) for _ in range(2)]
+            self._out_host = [torch.empty(self.loss.shape, dtype=self.loss.dtype).pin_memory() for _ in range(2)]
+            self._out_ready = [torch.cuda.Event() for _ in range(2)]
+            self._out_done = [torch.cuda.Event() for _ in range(2)]
+            self._j = 0
+        j = self._j
+        self._j ^= 1
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._out_done[j])             # the copy that last read this staging buffer is over
+        self._out_stage[j].copy_(self.loss, non_blocking=True)
+        self._out_ready[j].record(cur)
+        with torch.cuda.stream(self._down):
+            self._down.wait_event(self._out_ready[j])
+            self._out_host[j].copy_(self._out_stage[j], non_blocking=True)
+            self._out_done[j].record(self._down)
+        return CapturedStep._Download(self._out_host[j], self._out_done[j])
 
 
 def used_parameter_names(model_name):
