@@ -159,7 +159,10 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
     rvar[c] = (1.f - momentum) * rvar[c] + momentum * (float)unb;
   }
 }
-__global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
+// U pixels in flight per thread: 2 with a residual stream (64 B outstanding), 4 without -- with one input
+// stream two 16-byte loads per thread at 768 threads/SM left HBM3e under-subscribed (3.7 of ~5.5 TB/s).
+template <int U, bool RES>
+__global__ void __launch_bounds__(256, 3) bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
                                                        bf16* __restrict__ y, const float* __restrict__ mean,
                                                        const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                        const float* __restrict__ beta, long long P, int C, int ldx,
@@ -173,26 +176,32 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const bf16* __restrict__ 
     sc[j] = rstd[c] * gamma[c];
     sh[j] = beta[c] - mean[c] * sc[j];
   }
-  HN_COL_LOOP2(it, P) {
-    const long long pix2 = pix + it.pstride;
-    const bool two = pix2 < P;
-    float f[2][8], r[2][8];
-    load8(x + pix * ldx + it.cv * 8, f[0]);
-    if (two) load8(x + pix2 * ldx + it.cv * 8, f[1]);
-    if (res) {
-      load8(res + pix * ldr + it.cv * 8, r[0]);
-      if (two) load8(res + pix2 * ldr + it.cv * 8, r[1]);
+  for (long long pix = it.pix0; pix < P; pix += (long long)U * it.pstride) {
+    float f[U][8], r[RES ? U : 1][8];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long pu = pix + (long long)u * it.pstride;
+      if (pu < P) load8(x + pu * ldx + it.cv * 8, f[u]);
+    }
+    if (RES) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long pu = pix + (long long)u * it.pstride;
+        if (pu < P) load8(res + pu * ldr + it.cv * 8, r[u]);
+      }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (u == 1 && !two) break;
+    for (int u = 0; u < U; ++u) {
+      const long long pu = pix + (long long)u * it.pstride;
+      if (pu < P) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float v = fmaf(f[u][j], sc[j], sh[j]);
-        if (res) v += r[u][j];
-        f[u][j] = apply_act(v, act);
+        for (int j = 0; j < 8; ++j) {
+          float v = fmaf(f[u][j], sc[j], sh[j]);
+          if (RES) v += r[RES ? u : 0][j];
+          f[u][j] = apply_act(v, act);
+        }
+        store8(y + pu * ldy + it.cv * 8, f[u]);
       }
-      store8(y + (u ? pix2 : pix) * ldy + it.cv * 8, f[u]);
     }
   }
 }
@@ -339,7 +348,8 @@ extern "C" int hn_bn_finalize(const float* sum, const float* sqsum, long long co
 extern "C" int hn_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd, const float* gamma, const float* beta, long long P, int C, int ldx, int ldr, int ldy, int act, void* stream) {
   REQ_CV(C, "bn_apply");
   HN_REQUIRE(x && y && mean && rstd && gamma && beta, "bn_apply: null");
-  bn_apply_kernel<<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (const bf16*)res, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act);
+  if (res) bn_apply_kernel<2, true><<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (const bf16*)res, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act);
+  else bn_apply_kernel<4, false><<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, nullptr, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act);
   HN_CHECK_LAUNCH("bn_apply");
   return HN_OK;
 }
