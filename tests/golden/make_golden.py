@@ -106,6 +106,35 @@ def main():
         keys[name] = {k: list(v.shape) for k, v in sd.items()}
     with open(os.path.join(HERE, "state_dict_keys.json"), "w") as f:
         json.dump(keys, f, indent=0)
+    make_trained(classes)
+
+
+def make_trained(classes):
+    """Pin of the trained-weights recipe (tests/golden/trained.py): the recipe run through the REAL reference
+    classes; for the bytecode-only Autoencoder32K family through the oracle (unpinned)."""
+    from tests.golden import trained
+    for name, cls in classes.items():
+        model = cls()
+        model.load_state_dict(nets.init_state_dict(name, 0), strict=True)
+        losses, _ = trained.train_module(model, name)
+        sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        x, _ = trained.blobs(2, trained.S, trained.EVAL_SEED)
+        with torch.no_grad():
+            out = model(x)
+        out = out[-1] if isinstance(out, tuple) else out
+        fx = trained.summary(sd, losses, out)
+        fx["source"] = "reference classes"
+        torch.save(fx, os.path.join(HERE, f"trained_{name}.pt"))
+        print("trained", name, [round(l, 4) for l in losses[::5]], "frac>0.5", float((out > 0.5).float().mean()))
+    for name in ("ae32k_image", "latent2mask"):
+        sd, losses = trained.train_oracle(name)
+        x, _ = trained.blobs(2, trained.S, trained.EVAL_SEED)
+        with torch.no_grad():
+            out = nets.FORWARDS[name](sd, x, nets.Ctx(training=True, dropout="off"))
+        fx = trained.summary(sd, losses, out)
+        fx["source"] = "oracle/nets.py (no reference source for this family: parity unpinned)"
+        torch.save(fx, os.path.join(HERE, f"trained_{name}.pt"))
+        print("trained", name, [round(l, 4) for l in losses[::5]])
 
 
 if __name__ == "__main__":

@@ -77,3 +77,35 @@ def test_ae32k_shapes():
     sdm = nets.init_state_dict("latent2mask", 0)
     y = nets.FORWARDS["latent2mask"](sdm, x, ctx)
     assert y.shape == (1, 1, 64, 64) and 0 <= float(y.min()) and float(y.max()) <= 1
+
+
+@pytest.mark.parametrize("name", ["unet", "autoencoder", "i2i2m", "fct", "ae32k_image", "latent2mask"])
+def test_trained_recipe_matches_reference_pin(name):
+    """The trained-weights fixture (tests/golden/trained.py): the oracle run through the recipe must retrace
+    what the unmodified reference classes did under the same recipe (make_golden.py) -- loss trajectory,
+    per-tensor norms of the trained weights and the trained net's output on a fixed batch.  fp32 vs fp32 on
+    the CPU over 20-60 AdamW steps: agreement is ~1e-5; the bounds leave room for thread-count dependent
+    summation order.  (Autoencoder32K family: the pin is the oracle's own run -- parity unpinned.)"""
+    from tests.golden import trained
+    fx = torch.load(os.path.join(G, f"trained_{name}.pt"))
+    assert fx["recipe"]["steps"] == trained.STEPS[name]
+    sd, losses = trained.train_oracle(name)
+    assert len(losses) == len(fx["losses"])
+    # The first 20 steps retrace the reference to ~1e-6.  FCT / Image2Image2Mask run 60 steps (their masks need
+    # them to straddle 0.5) and lr 1e-3 without warm-up is a chaotic trajectory: a 1e-7 summation-order
+    # difference at step 8 grows to 1e-2 in the loss by step 45 (measured here, oracle vs reference classes,
+    # both fp32 on the same CPU), so beyond step 20 only the first 20 steps and the fixture's purpose are checked.
+    for i, (a, b) in enumerate(zip(losses, fx["losses"])):
+        if i < 20:
+            assert abs(a - b) <= 2e-4, (i, a, b)
+    x, _ = trained.blobs(2, trained.S, trained.EVAL_SEED)
+    with torch.no_grad():
+        out = nets.FORWARDS[name](sd, x, nets.Ctx(training=True, dropout="off"))
+    out = out[-1] if isinstance(out, tuple) else out
+    if trained.STEPS[name] <= 20:
+        for k, n in fx["norms"].items():
+            assert abs(float(sd[k].float().norm()) - n) <= 2e-3 * max(n, 1e-2), k
+        assert (out - fx["eval_out"]).abs().max().item() <= 2e-2
+    if name not in trained.RECONSTRUCTION:       # the fixture's purpose: masks that straddle the 0.5 threshold
+        frac = float((out > 0.5).float().mean())
+        assert 0.02 < frac < 0.98, frac
