@@ -246,6 +246,41 @@ int hn_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_av
                   long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
                   int step, float grad_scale, void* stream);
 
+/* same update with the step count kept on the device: step_dev[0] = steps done so far (the kernel derives the
+ * bias corrections from it and the last CTA bumps it), step_dev[1] = scratch counter (zero).  This is the form a
+ * CUDA graph can replay (torch.optim.AdamW.step, FCT.py:338, under parallel.CapturedStep).           */
+int hn_adamw_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                      long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                      long long* step_dev, float grad_scale, void* stream);
+
+/* ---- losses / metrics: the step right after forward -------- */
+/* All tensors NCHW fp32 as the reference's modules return them.  ws = float[16], zero before the first call
+ * (self-cleaning afterwards).  One launch each: the last CTA reduces, writes the scalar, keeps what backward needs. */
+/* DiceLoss.forward, Metrics.py:14-22: 1 - (2 sum(p t) + smooth) / (sum p + sum t + smooth) on channel 0 */
+int hn_dice_fwd(const float* pred, const float* target, int B, int Cpred, int Ctarget, int HW, float smooth,
+                float* ws, float* loss3 /* {loss, sum(p t), sum p + sum t + smooth} */, void* stream);
+/* dL/dpred [B,Cpred,H,W] (zero outside channel 0); fwd_out3 = loss3 of the forward; grad_out = device scalar or NULL (= 1) */
+int hn_dice_bwd(const float* target, const float* fwd_out3, const float* grad_out, float* dpred, int B, int Cpred,
+                int Ctarget, int HW, float smooth, void* stream);
+/* nn.MSELoss (Model.py:57 L2 term): out2[0] = mean((a-b)^2), out2[1] = PSNR = 20 log10(1/sqrt(mse)) (Model.py:30) */
+int hn_mse_fwd(const float* a, const float* b, long long n, float* ws, float* out2, void* stream);
+int hn_mse_bwd(const float* a, const float* b, long long n, const float* grad_out, float* da, void* stream);
+/* JaccardScore.forward, Metrics.py:31-39: sum(p!=0 & t!=0) / sum(p!=0 | t!=0) on channel 0 (NaN for an empty union) */
+int hn_jaccard(const float* pred, const float* target, int B, int Cpred, int Ctarget, int HW, float* ws,
+               float* out, void* stream);
+
+/* ---- input pipeline: the step right before forward --------- */
+/* Dataloader.py:16-24 (ToTensor: uint8 HWC -> float/255) + Model.py:44-53 (batch hflip | image + N(0,std^2) noise
+ * and up to four patch_size x patch_size blackout patches at rows patch_x / columns patch_y) in one pass.
+ * src: uint8 [B,H,W,3] (src_is_u8) or fp32 [B,3,H,W].  Writes dst_nhwc (bf16 [B,H,W,ld], channels 3..7 zero: the
+ * first conv's operand) and/or dst_nchw (fp32 [B,3,H,W]).  noise_std > 0 selects the noise branch, which -- as in
+ * the reference -- starts from the UNFLIPPED image.  step_counter (device, may be NULL) is mixed into the seed. */
+int hn_augment_pack(const void* src, int src_is_u8, void* dst_nhwc, float* dst_nchw, int B, int H, int W, int ld,
+                    int flip, float noise_std, unsigned long long seed, const unsigned long long* step_counter,
+                    int npatch, const int* patch_x, const int* patch_y, int patch_size, void* stream);
+/* AvgPool2d(2,2) backward: dx[2h+i, 2w+j] = dy[h, w] / 4; H, W = extent of dy */
+int hn_avgpool2_bwd(const void* dy, void* dx, int B, int H, int W, int C, int lddy, int lddx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

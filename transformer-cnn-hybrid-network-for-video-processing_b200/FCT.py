@@ -14,7 +14,7 @@ from .layers import Conv2d, LayerNorm, MultiheadAttention
 def _io(fn):
     """Public ``forward``: NCHW fp32 in/out around the NHWC bf16 implementation."""
     def wrapped(self, *xs):
-        ys = fn(self, *[ops.to_nhwc(x) if torch.is_tensor(x) else x for x in xs])
+        ys = fn(self, *[ops.to_nhwc(x) if (torch.is_tensor(x) or isinstance(x, ops.PackedFrames)) else x for x in xs])
         return ops.to_nchw(ys, self._out_channels)
     return wrapped
 

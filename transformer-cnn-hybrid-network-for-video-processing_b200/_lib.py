@@ -76,6 +76,14 @@ SIGNATURES = {
     "hn_conv_wgrad_tc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _FP, _L, _P],
     "hn_conv_wgrad_tc_workspace": [POINTER(HnConv), _L],
     "hn_adamw_step": [_FP, _FP, _FP, _FP, _L, _F, _F, _F, _F, _F, _I, _F, _P],
+    "hn_adamw_step_dev": [_FP, _FP, _FP, _FP, _L, _F, _F, _F, _F, _F, _P, _F, _P],
+    "hn_dice_fwd": [_FP, _FP, _I, _I, _I, _I, _F, _FP, _FP, _P],
+    "hn_dice_bwd": [_FP, _FP, _FP, _FP, _I, _I, _I, _I, _F, _P],
+    "hn_mse_fwd": [_FP, _FP, _L, _FP, _FP, _P],
+    "hn_mse_bwd": [_FP, _FP, _L, _FP, _FP, _P],
+    "hn_jaccard": [_FP, _FP, _I, _I, _I, _I, _FP, _FP, _P],
+    "hn_augment_pack": [_P, _I, _P, _FP, _I, _I, _I, _I, _I, _F, c_ulonglong, _P, _I, POINTER(c_int), POINTER(c_int), _I, _P],
+    "hn_avgpool2_bwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
 }
 
 _LONG_RESULT = {"hn_conv_wgrad_tc_workspace"}

@@ -43,6 +43,8 @@ class ConvTranspose2d(nn.ConvTranspose2d):
 class BatchNorm2d(nn.BatchNorm2d):
     def nhwc(self, x, act="none", res=None):
         training = self.training or self.running_mean is None
+        if training:
+            ops._fold_cache.pop(id(self), None)        # running statistics are about to move (raw-pointer update)
         if training and self.num_batches_tracked is not None:
             self.num_batches_tracked.add_(1)
         return ops.bn_act(x, self.weight, self.bias, self.running_mean, self.running_var, training, res=res,

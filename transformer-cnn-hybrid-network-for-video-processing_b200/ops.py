@@ -160,8 +160,24 @@ class _ToNCHW(torch.autograd.Function):
         return dx, None
 
 
+class PackedFrames:
+    """A batch already in the first conv's operand layout (NHWC bf16, channels padded to 8) -- what
+    ``hybridnet.data`` produces on the device; the model forwards accept it in place of the NCHW fp32 tensor."""
+    __slots__ = ("nhwc", "channels")
+
+    def __init__(self, nhwc_tensor, channels=3):
+        self.nhwc, self.channels = nhwc_tensor, channels
+
+    @property
+    def shape(self):
+        B, H, W, _ = self.nhwc.shape
+        return torch.Size((B, self.channels, H, W))
+
+
 def to_nhwc(x):
     """[B,C,H,W] fp32 -> [B,H,W,pad8(C)] bf16 (x.to(device) boundary, FCT.py:326)."""
+    if isinstance(x, PackedFrames):
+        return x.nhwc
     return _ToNHWC.apply(x)
 
 
@@ -169,13 +185,28 @@ def to_nchw(x, C):
     return _ToNCHW.apply(x, C)
 
 
+class _AvgPool2Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x, ld = nhwc(x)
+        B, H, W, C = x.shape
+        y = _new(B, H // 2, W // 2, C, x)
+        call("hn_avgpool2_fwd", x.data_ptr(), y.data_ptr(), B, H, W, C, ld, C, _stream())
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy, ld = nhwc(dy)
+        B, H, W, C = dy.shape
+        dx = _new(B, 2 * H, 2 * W, C, dy)
+        call("hn_avgpool2_bwd", dy.data_ptr(), dx.data_ptr(), B, H, W, C, ld, C, _stream())
+        return dx
+
+
 def avgpool2(x):
-    """AvgPool2d(2,2) of the input pyramid (FCT.py:238-240); the RGB frames carry no grad."""
-    x, ld = nhwc(x.detach())
-    B, H, W, C = x.shape
-    y = _new(B, H // 2, W // 2, C, x)
-    call("hn_avgpool2_fwd", x.data_ptr(), y.data_ptr(), B, H, W, C, ld, C, _stream())
-    return y
+    """AvgPool2d(2,2) of the input pyramid (FCT.py:238-240).  Differentiable like nn.AvgPool2d; the backward
+    pass is only recorded when the frames require grad (they do not in the reference's trainers)."""
+    return _AvgPool2Fn.apply(x)
 
 
 # ----------------------------------------------------------------------------
@@ -196,7 +227,14 @@ def _packed(w, kind, Cpad):
     oid = id(owner)
     ent = _pack_cache.get(oid)
     ver = (owner._version, owner.data_ptr())
-    if ent is None or ent["ref"]() is not owner or ent.get("ver") != ver:
+    if ent is not None and ent["ref"]() is owner and ent.get("ver") != ver and ent["ver"][1] == ver[1]:
+        # the weights changed in place (optimizer step, load_state_dict): refresh the EXISTING buffers.  Their
+        # device addresses may be baked into a captured CUDA graph and into the hn_pack_weight_multi job table,
+        # so the allocations are never replaced while the parameter's storage stays where it is.
+        for job in ent.get("jobs", {}).values():
+            _run_pack_job(job)
+        ent["ver"] = ver
+    elif ent is None or ent["ref"]() is not owner or ent.get("ver") != ver:
         ent = {"ver": ver, "ref": weakref.ref(owner, lambda _r, oid=oid: _pack_cache.pop(oid, None))}
         _pack_cache[oid] = ent
     if key in ent:
@@ -243,6 +281,14 @@ def _packed(w, kind, Cpad):
     return ent[key]
 
 
+def _run_pack_job(job):
+    """Re-run one recorded pack (same source, same destination buffer)."""
+    if job[15] and job[9] == 1 and job[5] == 0:        # hn_pack_weight_s2dgrad job: [src, buf, d0, Npad, d1, 0,0,0, Kpad, 1,0,0,0,0,0, KH]
+        call("hn_pack_weight_s2dgrad", job[0], job[1], job[2], job[4], job[15], _stream())
+    else:                                              # [src, buf, N, Npad, Creal, Cpad, kh, kw, Kpad, a0..a5, 0]
+        call("hn_pack_weight", job[0], job[1], job[2], job[4], job[5], job[6], job[7], *job[9:15], _stream())
+
+
 _repack_table = {"sig": None, "dev": None, "n": 0, "max": 1}
 
 
@@ -276,9 +322,11 @@ def repack_all():
 
 
 def invalidate_packed():
-    """Drop every derived bf16 weight copy (call after an optimizer step that bypasses ``_version``,
-    or to make a benchmark pay for the repack each step like real training does)."""
-    _pack_cache.clear()
+    """Mark every derived bf16 weight copy stale (call after an optimizer step that bypasses ``_version``, or to
+    make a benchmark pay for the repack each step like real training does).  The buffers are kept and refilled in
+    place on next use: a captured CUDA graph may hold their addresses."""
+    for ent in _pack_cache.values():
+        ent["ver"] = (None, ent["ver"][1])
 
 
 def _desc(**kw):
@@ -733,6 +781,9 @@ def conv_bn_act(x, weight, bias, bn, *, x2=None, res=None, stride=1, pad=1, dil=
         wf, bf = _folded_eval_bn(weight, bias, bn, transposed)
         return conv2d(x, wf, bf, x2=x2, stride=stride, pad=pad, dil=dil, ups=ups, act=act, transposed=transposed)
     if training:
+        # hn_bn_finalize moves the running statistics through raw pointers (no ``_version`` bump): whatever was
+        # folded for inference from the old statistics is stale from here on
+        _fold_cache.pop(id(bn), None)
         z, s0, s1 = _ConvStatsFn.apply(x, x2, weight, bias, stride, pad, dil, ups, transposed)
         stats = (s0, s1)
     else:

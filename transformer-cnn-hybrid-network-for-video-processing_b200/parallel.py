@@ -29,9 +29,15 @@ class GradArena:
         for p in self.params:
             self.slices.append((off, off + p.numel()))
             off += (p.numel() + 3) // 4 * 4
-        # buckets over the REVERSED parameter list (backward order), equal element counts
+        # buckets over the REVERSED parameter list (backward order).  Sizes shrink geometrically (1/2, 1/4, ...):
+        # the all-reduce of the LAST bucket cannot overlap anything (backward is over when it starts), so it is
+        # the smallest one -- its exposed tail is what the 8-GPU step pays over the 1-GPU step
         order = list(range(len(self.params)))[::-1]
-        per = max(1, n // max(1, buckets))
+        nb = max(1, buckets)
+        cuts, acc = [], 0.0
+        for j in range(nb - 1):
+            acc += 0.5 ** (j + 1)
+            cuts.append(acc * n)
         self.bucket_of = {}
         self.bucket_range = []
         cur, lo, hi, b = 0, None, None, 0
@@ -41,9 +47,9 @@ class GradArena:
             hi = e if hi is None else max(hi, e)
             self.bucket_of[i] = b
             cur += e - s
-            if cur >= per and b < buckets - 1:
+            if b < nb - 1 and cur >= cuts[b]:
                 self.bucket_range.append((lo, hi))
-                b, cur, lo, hi = b + 1, 0, None, None
+                b, lo, hi = b + 1, None, None
         if lo is not None:
             self.bucket_range.append((lo, hi))
         self.bucket_size = [0] * len(self.bucket_range)
@@ -52,11 +58,19 @@ class GradArena:
         self.pending = list(self.bucket_size)
         self.comm = torch.cuda.Stream(device=dev) if dev.type == "cuda" else None
         self.works = []
+        self.scale_in_finish = True   # optim.AdamW folds the 1/world into its update and clears this
+        self._written = set()         # parameters whose gradient a kernel already reduced into the arena this step
+        self._counted = set()         # parameters already counted towards their bucket this step
         self._attach()
         self._hooks = [self._make_hook(i) for i in range(len(self.params))]
         if self.world > 1:
             for i, p in enumerate(self.params):
                 p.register_post_accumulate_grad_hook(self._hooks[i])
+        self.rebind()
+
+    def rebind(self):
+        """Refresh the parameter-address table (after the parameters' storage moved, e.g. optim.AdamW re-pointing
+        them into its flat buffer)."""
         self._by_ptr = {p.data_ptr(): i for i, p in enumerate(self.params)}
 
     def direct(self, on=True):
@@ -70,11 +84,18 @@ class GradArena:
             return self
 
         def sink(ptr, numel):
+            # The kernels use the slice both as the accumulator AND (BatchNorm backward) as this call's reduction
+            # result, which is only right while the slice still holds the zeros of ``zero_grad``.  A second write
+            # in the same step (gradient accumulation over micro-batches, a second backward, a module applied
+            # twice) therefore gets None: that call reduces into scratch and autograd accumulates it.
             i = self._by_ptr.get(ptr)
-            if i is None:
+            if i is None or i in self._written:
                 return None
             s, e = self.slices[i]
-            return self.arena[s:e] if e - s == numel else None
+            if e - s != numel:
+                return None
+            self._written.add(i)
+            return self.arena[s:e]
 
         def done(ptr):
             i = self._by_ptr[ptr]
@@ -94,11 +115,19 @@ class GradArena:
         self._attach()
         self.pending = list(self.bucket_size)
         self.works = []
+        self._written.clear()
+        self._counted.clear()
 
     def _make_hook(self, i):
         def hook(_p):
             if not self.exchange:
                 return
+            if i in self._counted:
+                # a second gradient for the same parameter after its bucket may already be in flight: the
+                # all-reduce would miss it.  Accumulate micro-batches with ``exchange = False`` and switch it on
+                # for the last one (DDP's no_sync), or call zero_grad() between backward passes.
+                raise RuntimeError("hybridnet.GradArena: parameter received a second gradient in one exchanged step")
+            self._counted.add(i)
             b = self.bucket_of[i]
             self.pending[b] -= 1
             if self.pending[b] == 0:
@@ -127,7 +156,8 @@ class GradArena:
             w.wait()
         if self.comm is not None:
             torch.cuda.current_stream().wait_stream(self.comm)
-        self.arena.mul_(1.0 / self.world)
+        if self.scale_in_finish:      # otherwise optim.AdamW applies 1/world inside its update kernel
+            self.arena.mul_(1.0 / self.world)
 
 
 class CapturedStep:
