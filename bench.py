@@ -1,12 +1,14 @@
 #!/usr/bin/env python
 """Headline benchmark: train frames/sec (fwd+bwd, 256x256) of the hybrid segmentation nets.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload ae32k_image|fct|unet|...]
-  python bench.py --impl reference ...      # the reference's CPU arithmetic on the host cores
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload fct|unet|ae32k_image|...]
+  python bench.py --impl reference ...      # the reference's own classes on the host cores (oracle/_ref)
 
 Own arm: one process per GPU (torchrun sets RANK/LOCAL_RANK/WORLD_SIZE); a step is
-zero_grad -> forward -> loss -> backward (-> NCCL gradient all-reduce when N>1) over one batch of
-synthetic frames; weights are re-packed every step as in real training.  One JSON line on rank 0.
+zero_grad -> forward -> loss -> backward (-> NCCL gradient all-reduce when N>1) -> fused AdamW (+ weight repack)
+over one batch of synthetic frames.  One JSON line on rank 0.  The default workload is FCT, batch 32 =
+two 16-frame clips per GPU (BASELINE configs[2] / configs[4]); at N=1 the same line carries UNet B=32 and
+Autoencoder32K B=16 under "extra", each with its own roofline / e2e / cpu_baseline, timed in the same run.
 """
 import argparse
 import contextlib
@@ -24,14 +26,19 @@ import torch  # noqa: E402
 
 # workload -> (model key, per-GPU batch, loss, reference/BASELINE config string)
 WORKLOADS = {
-    "ae32k_image": ("ae32k_image", 16, "mse", "Autoencoder32K('image') 256->32K-latent image2image, fwd+bwd (BASELINE configs[1])"),
-    "fct": ("fct", 32, "dice", "FCT conv-attention net, batch 32, fwd+bwd (BASELINE configs[2])"),
+    "fct": ("fct", 32, "dice", "FCT conv-attention net, 2 x 16-frame clips (batch 32) per GPU, fwd+bwd (BASELINE configs[2], configs[4])"),
     "unet": ("unet", 32, "dice", "UNet fwd+bwd (BASELINE configs[0] shape on GPU)"),
+    "ae32k_image": ("ae32k_image", 16, "mse", "Autoencoder32K('image') 256->32K-latent image2image, fwd+bwd (BASELINE configs[1])"),
     "autoencoder": ("autoencoder", 64, "mse", "AutoEncoder (8K latent) fwd+bwd"),
     "i2i2m": ("i2i2m", 16, "dice", "Image2Image2Mask (AE -> UNet) fwd+bwd (BASELINE configs[3] ii)"),
     "latent2mask": ("latent2mask", 16, "dice", "latent-to-mask: frozen Encoder_32K -> Decoder_32K('mask') training (BASELINE configs[3] i)"),
 }
-DEFAULT_WORKLOAD = "ae32k_image"
+DEFAULT_WORKLOAD = "fct"
+EXTRA_WORKLOADS = ("unet", "ae32k_image")     # carried under "extra" by the default N=1 line
+CLIP_FRAMES = 16                              # BASELINE configs[4]: 16-frame clips
+# frames per step of the CPU arm (bounded sample: FCT B=32 would need ~60 s and >10 GB per step on 16 cores)
+CPU_FRAMES = {"fct": 1, "unet": 4, "ae32k_image": 2, "autoencoder": 8, "i2i2m": 2, "latent2mask": 2}
+LR = 1e-4
 MUFU_TEXP_S = 4.647        # ex2.approx results/s (x1e12), scripts/mufu_bench.cu on B200 @ 1965 MHz
 
 
@@ -101,11 +108,12 @@ def make_batch(B, seed, device, pinned=False):
 
 
 def loss_fn(kind, out, x, y):
+    """Reference formulas in plain torch (CPU arm, torch-eager bar): nn.MSELoss / DiceLoss (Metrics.py:14-22)."""
     out = out[-1] if isinstance(out, tuple) else out
     if kind == "mse":
         return torch.nn.functional.mse_loss(out, x)
-    p, t = out[:, 0].reshape(-1), y[:, 0].reshape(-1)          # DiceLoss, Metrics.py:14-22
-    return 1.0 - (2.0 * torch.dot(p, t) + 1.0) / (p.sum() + t.sum() + 1.0)
+    p, t = out[:, 0].reshape(-1), y[:, 0].reshape(-1)
+    return 1.0 - (2.0 * (p * t).sum() + 1.0) / (p.sum() + t.sum() + 1.0)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -235,97 +243,133 @@ def roofline_from(agg, steps, peaks):
 # reference arm / cpu baseline: the oracle (CPU restatement of the reference's PyTorch path)
 # ---------------------------------------------------------------------------------------------
 def cpu_reference(workload, frames, steps, warmup, infer=False):
-    """fwd+bwd of the reference arithmetic (oracle/nets.py, fp32, all host cores) on `frames` frames."""
-    from oracle import nets
+    """The same step on the host cores, fp32, all threads.  FCT / UNet / AutoEncoder / Image2Image2Mask: the
+    reference's UNMODIFIED classes (oracle/_ref, staged by oracle/make_ref.py) with the reference's DiceLoss /
+    nn.MSELoss and torch.optim.AdamW -> kind "reference".  Autoencoder32K family (bytecode only in the reference):
+    the oracle port -> kind "port".  Returns (frames/s, s/step, cores, kind)."""
+    from oracle import nets, ref_loader
     key, _, kind, _ = WORKLOADS[workload]
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    x, y = make_batch(frames, 1, "cpu")
+    times = []
+    if ref_loader.available() and key in ("fct", "unet", "autoencoder", "i2i2m"):
+        classes, RefDice = ref_loader.load()
+        torch.manual_seed(0)
+        model = classes[key]()
+        model.train(not infer)
+        crit = RefDice() if kind == "dice" else torch.nn.MSELoss()
+        opt = torch.optim.AdamW(model.parameters(), lr=LR)
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            if infer:
+                with torch.no_grad():
+                    model(x)
+            else:
+                opt.zero_grad()
+                out = model(x)
+                out = out[-1] if isinstance(out, tuple) else out
+                loss = crit(out, y if kind == "dice" else x)
+                loss.backward()
+                opt.step()
+            if i >= warmup:
+                times.append(time.perf_counter() - t0)
+        sec = sum(times) / len(times)
+        return frames / sec, sec, cores, "reference"
     sd = nets.init_state_dict(key, 0)
     frozen = (lambda k: k.startswith("0.")) if key == "latent2mask" else (lambda k: False)
     params = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running" not in k and not frozen(k) else v)
               for k, v in sd.items()}
-    x, y = make_batch(frames, 1, "cpu")
+    opt = torch.optim.AdamW([p for p in params.values() if p.requires_grad], lr=LR)
     ctx = nets.Ctx(training=not infer, dropout="off" if infer else "on")
-    times = []
     for i in range(warmup + steps):
-        for p in params.values():
-            if p.requires_grad:
-                p.grad = None
         t0 = time.perf_counter()
         if infer:
             with torch.no_grad():
                 nets.FORWARDS[key](params, x, ctx)
         else:
+            opt.zero_grad()
             out = nets.FORWARDS[key](params, x, ctx)
             loss_fn(kind, out, x, y).backward()
+            opt.step()
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     sec = sum(times) / len(times)
-    return frames / sec, sec, cores
+    return frames / sec, sec, cores, "port"
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
-    ap.add_argument("--batch", type=int, default=0, help="frames per GPU (default: the workload's)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-dropout", action="store_true")
-    ap.add_argument("--kernel-table", action="store_true", help="print the per-kernel time table to stderr")
-    ap.add_argument("--kernel-detail", action="store_true", help="per conv geometry rows in the kernel table")
-    ap.add_argument("--infer", action="store_true", help="eval-mode forward only (BASELINE configs[3] inference leg); "
-                    "e2e copies the whole output back to pinned host memory")
-    ap.add_argument("--no-graph", action="store_true", help="issue every kernel eagerly instead of replaying the captured step")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+def cpu_sample_text(kind_impl, frames, steps, infer, sec):
+    src = ("the reference's unmodified classes from oracle/_ref (torch fp32 CPU)" if kind_impl == "reference"
+           else "oracle port of the reference's PyTorch path (torch fp32 CPU; the reference ships this family as bytecode only)")
+    what = "fwd" if infer else "zero_grad+fwd+loss+bwd+AdamW"
+    return f"{frames} frames x {steps} timed {what} steps of the same net, {src}, {sec:.2f} s/step"
 
-    rank = int(os.environ.get("RANK", 0))
-    world = int(os.environ.get("WORLD_SIZE", 1))
-    local = int(os.environ.get("LOCAL_RANK", 0))
-    key, B0, kind, cfg_name = WORKLOADS[args.workload]
-    B = args.batch or B0
-    metric, unit = "train frames/sec (fwd+bwd, 256x256)", "frames/s"
-    if args.infer:
-        metric = "inference frames/sec (eval-mode fwd, 256x256)"
-    config = {"workload": cfg_name, "frames_per_gpu": B, "global_batch": B * world, "frame": "3x256x256 fp32 in [0,1)",
-              "parallelism": f"dp{world}" if world > 1 else "single", "l2": "activations per step >> 126 MB L2 (no flush needed)"}
 
-    if args.impl == "reference":
-        if rank != 0:
-            return
-        frames = 2 if key in ("fct", "ae32k_image", "latent2mask", "i2i2m") else 4
-        steps = max(1, min(args.steps, 3))
-        fps, sec, cores = cpu_reference(args.workload, frames, steps, 1, args.infer)
-        sample = f"{frames} frames x {steps} timed {'fwd' if args.infer else 'fwd+bwd'} passes of the same net (oracle port of the reference's PyTorch path, fp32)"
-        print(json.dumps({"impl": "reference", "metric": metric, "value": round(fps, 4), "unit": unit, "n_gpus": args.gpus,
-                          "steps": steps, "warmup": 1, "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True,
-                          "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                          "cpu_baseline": {"value": round(fps, 4), "unit": unit, "cores": cores, "kind": "port", "sample": sample},
-                          "e2e": {"value": round(fps, 4), "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
-        return
+def torch_eager_bar(key, kind, B, dev, steps=5, warmup=2):
+    """The library bar: the same modules with torch eager on this B200 --
+    cuDNN / cuBLAS / SDPA, fp32 and bf16 autocast + channels_last -- same batch, same step definition.  A stated
+    baseline, never the product path.  frames/s per variant, or the error text."""
+    from oracle import nets, ref_loader
+    out = {}
+    x, y = make_batch(B, 1, dev)
+    for variant in ("fp32", "bf16_autocast_channels_last"):
+        try:
+            torch.manual_seed(0)
+            if ref_loader.available() and key in ("fct", "unet", "autoencoder", "i2i2m"):
+                classes, _ = ref_loader.load()
+                model = classes[key]().to(dev).train()
+                fwd = lambda xx: model(xx)
+                params = list(model.parameters())
+                if variant != "fp32":
+                    model = model.to(memory_format=torch.channels_last)
+            else:
+                sd = nets.init_state_dict(key, 0)
+                frozen = (lambda k: k.startswith("0.")) if key == "latent2mask" else (lambda k: False)
+                pd = {k: (v.to(dev).requires_grad_(True) if v.is_floating_point() and "running" not in k and not frozen(k)
+                          else v.to(dev)) for k, v in sd.items()}
+                ctx = nets.Ctx(training=True, dropout="on")
+                fwd = lambda xx: nets.FORWARDS[key](pd, xx, ctx)
+                params = [p for p in pd.values() if p.requires_grad]
+            opt = torch.optim.AdamW(params, lr=LR)
+            xx = x if variant == "fp32" else x.contiguous(memory_format=torch.channels_last)
 
+            def one():
+                opt.zero_grad(set_to_none=True)
+                if variant == "fp32":
+                    o = fwd(xx)
+                else:
+                    with torch.autocast("cuda", dtype=torch.bfloat16):
+                        o = fwd(xx)
+                o = o[-1] if isinstance(o, tuple) else o
+                loss_fn(kind, o.float(), x, y).backward()
+                opt.step()
+            for _ in range(warmup):
+                one()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                one()
+            e1.record()
+            torch.cuda.synchronize()
+            out[variant] = round(B * steps / (e0.elapsed_time(e1) / 1e3), 1)
+            del opt, params
+        except Exception as e:      # e.g. out of memory for a materialised 16384^2 attention
+            out[variant] = f"failed: {type(e).__name__}: {str(e)[:120]}"
+        torch.cuda.empty_cache()
+    return out
+
+
+def run_ours(args, workload, B, rank, world, local, dev, steps, warmup, with_cpu, with_eager):
+    """One workload through the product: returns the result dict on rank 0 (None elsewhere)."""
     import torch.distributed as dist
     import hybridnet
     from hybridnet import _lib, ops, parallel
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        import datetime
-        # keep stdout to the one JSON line: NCCL writes its banner / log lines to fd 1 from C, so fd 1 is pointed
-        # at stderr for the whole run and the JSON line goes to the saved descriptor
-        sys.stdout.flush()
-        json_fd = os.dup(1)
-        os.dup2(2, 1)
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        if "HN_NCCL_DEBUG" in os.environ:
-            os.environ["NCCL_DEBUG"] = os.environ["HN_NCCL_DEBUG"]
-        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
-    else:
-        json_fd = None
-    _lib.call("hn_check_device")
+    key, _, kind, cfg_name = WORKLOADS[workload]
+    metric, unit = "train frames/sec (fwd+bwd, 256x256)", "frames/s"
+    if args.infer:
+        metric = "inference frames/sec (eval-mode fwd, 256x256)"
+    config = make_config(args, workload, B, world)
     torch.manual_seed(0)
     model = hybridnet.MODELS[key]().to(dev).train()
     if args.infer:
@@ -338,9 +382,10 @@ def main():
     dead = parallel.used_parameter_names(key)
     used = {n for n, p in model.named_parameters() if p.requires_grad and n not in dead}
     arena = parallel.GradArena(model, used=used, buckets=4).direct()     # kernels reduce dW / BN grads straight into the arena
+    opt = hybridnet.optim.AdamW(model.parameters(), arena, lr=LR)        # flat fused AdamW; folds the 1/world of the mean
+    crit = hybridnet.DiceLoss() if kind == "dice" else hybridnet.MSELoss()
     x, y = make_batch(B, 1 + rank, dev)
     xh, yh = make_batch(B, 1 + rank, dev, pinned=True)
-
     zero_cap = sum(p.numel() for p in model.parameters()) + (1 << 18)
 
     def infer_step(xd, yd):
@@ -351,13 +396,14 @@ def main():
     def step(xd, yd):
         if args.infer:
             return infer_step(xd, yd)
-        arena.zero_grad()
+        opt.zero_grad()                         # one memset of the gradient arena
         ops.begin_step(dev, zero_cap)           # all zero-initialised fp32 scratch of the step: one memset
-        ops.repack_all()                        # weights change every step in training: pay for the repack (one launch)
         out = model(xd)
-        loss = loss_fn(kind, out, xd, yd)
+        out = out[-1] if isinstance(out, tuple) else out
+        loss = crit(out, yd if kind == "dice" else xd)      # fused loss kernel (one launch), dL/dy seed kernel in backward
         loss.backward()
-        arena.finish()
+        arena.finish()                          # joins the bucketed NCCL all-reduce (sum)
+        opt.step()                              # fused AdamW over the flat arenas (x 1/world) + one-launch weight repack
         return loss
 
     def barrier():
@@ -366,7 +412,7 @@ def main():
         torch.cuda.synchronize()
 
     clocks = ClockSampler(local)                # streaming nvidia-smi, started ahead of the timed region
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step(x, y)
     barrier()
     # the public API for a training loop: the step recorded once as a CUDA graph, replayed per batch
@@ -376,21 +422,20 @@ def main():
     if not args.no_graph:
         captured = parallel.CapturedStep(step, x, y, warmup=1)
         run = captured
-        for _ in range(args.warmup):
+        for _ in range(warmup):
             run()
         barrier()
-    config["dispatch"] = "cuda-graph replay of the captured step" if captured else "eager"
     # ---- timed region 1: inputs resident in HBM ------------------------------------------------
     _lib.stats["launches"] = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with clocks:
         barrier()
         e0.record()
-        for _ in range(args.steps):
+        for _ in range(steps):
             loss = run() if captured else run(x, y)     # captured: the batch already sits in the static buffers
         e1.record()
         barrier()
-    launches = captured.launches * args.steps if captured else _lib.stats["launches"]
+    launches = captured.launches * steps if captured else _lib.stats["launches"]
     ms = e0.elapsed_time(e1)
     # ---- timed region 2: end to end through the public API with host buffers ---------------------
     barrier()
@@ -403,9 +448,9 @@ def main():
         # every step's H2D copy and D2H read are inside the timed region
         captured.prefetch(xh, yh)
         prev = None
-        for i in range(args.steps):
+        for i in range(steps):
             out = captured()
-            if i + 1 < args.steps:
+            if i + 1 < steps:
                 captured.prefetch(xh, yh)
             if args.infer:                         # the whole output (mask / reconstruction) comes back to the host
                 h = captured.download()
@@ -418,7 +463,7 @@ def main():
             out_host = prev.wait()
             last = float(out_host.view(-1)[0])
     else:
-        for _ in range(args.steps):
+        for _ in range(steps):
             xd = xh.to(dev, non_blocking=True)
             yd = yh.to(dev, non_blocking=True)
             out = step(xd, yd)
@@ -451,20 +496,22 @@ def main():
         _lib.set_profiler(None)
         agg = prof.table()
         roof = roofline_from(agg, psteps, peaks)
-        roof["traffic"], roof["traffic_source"] = ncu_traffic(args.workload, roof["kernel"])
+        roof["traffic"], roof["traffic_source"] = ncu_traffic(workload, roof["kernel"])
         if args.kernel_table:
             tot = sum(a["ms"] for a in agg.values())
+            print(f"---- {workload} (eager per-call CUDA events; launches under ~25 us carry the event floor)", file=sys.stderr)
             for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
                 print(f"{k:34s} {a['ms'] / psteps:9.3f} ms/step {100 * a['ms'] / tot:5.1f}%  n={a['n'] // psteps:4d}  "
                       f"{a['flops'] / max(a['ms'], 1e-9) / 1e9:8.1f} TFLOP/s {a['bytes'] / max(a['ms'], 1e-9) / 1e6:8.0f} GB/s",
                       file=sys.stderr)
         from oracle.nets import GFLOP_PER_FRAME
         gf = GFLOP_PER_FRAME[key][0 if args.infer else 1]
-        fps = B * world * args.steps / (ms / 1e3)
-        fps_e2e = B * world * args.steps / (ms_e2e / 1e3)
-        result = {"metric": metric, "value": round(fps, 2), "unit": unit, "n_gpus": world, "steps": args.steps,
-                  "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
-                  "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+        fps = B * world * steps / (ms / 1e3)
+        fps_e2e = B * world * steps / (ms_e2e / 1e3)
+        result = {"metric": metric, "value": round(fps, 2), "unit": unit, "n_gpus": world, "steps": steps,
+                  "warmup": warmup, "ms_per_step": round(ms / steps, 3), "higher_is_better": True,
+                  "scaling": "strong" if args.strong_clips else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                  "config": config, "dispatch": "cuda-graph replay of the captured step" if captured else "eager",
                   "clocks": clocks.summary(),
                   "e2e": {"value": round(fps_e2e, 2), "unit": unit,
                           "overlap": "H2D of batch i+1 (and D2H of output i-1 under --infer) on copy streams during step i" if captured else "none",
@@ -475,20 +522,131 @@ def main():
                   "model_tensor_roofline": {"GFLOP_per_frame_fwd" if args.infer else "GFLOP_per_frame_fwd_bwd": gf, "achieved_TFLOPs": round(fps / world * gf / 1e3, 2),
                                             "frac_of_sustained_bf16": round(fps / world * gf / 1e3 / peaks["tensor"], 4)},
                   "roofline": roof}
-        if world == 1 and not args.no_cpu_baseline:
-            frames = 2
-            cfps, sec, cores = cpu_reference(args.workload, frames, 2, 1, args.infer)
-            result["cpu_baseline"] = {"value": round(cfps, 4), "unit": unit, "cores": cores, "kind": "port",
-                                      "sample": f"{frames} frames x 2 timed {'fwd' if args.infer else 'fwd+bwd'} passes (oracle port of the reference's PyTorch path, fp32, {sec:.2f} s/pass)"}
+    # release this workload's device memory before the next one
+    ops.set_grad_sink(None, None)
+    ops.end_zero_pool()
+    if world > 1:
+        dist.barrier()
+    # the captured graph holds NCCL's persistent plans: it must die before the communicator does
+    del run, captured, step, infer_step, opt, arena, model, crit
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    if rank == 0 and with_eager:
+        result["torch_eager_b200"] = torch_eager_bar(key, kind, B, dev)
+    if rank == 0 and with_cpu:
+        frames = CPU_FRAMES[workload]
+        cfps, sec, cores, kimpl = cpu_reference(workload, frames, 2, 1, args.infer)
+        result["cpu_baseline"] = {"value": round(cfps, 4), "unit": unit, "cores": cores, "kind": kimpl,
+                                  "sample": cpu_sample_text(kimpl, frames, 2, args.infer, sec)}
+    return result
+
+
+def make_config(args, workload, B, world):
+    key, _, _, cfg_name = WORKLOADS[workload]
+    cfg = {"workload": cfg_name, "frames_per_gpu": B, "global_batch": B * world, "frame": "3x256x256 fp32 in [0,1)",
+           "parallelism": f"dp{world}" if world > 1 else "single",
+           "step": "eval forward" if args.infer else "zero_grad, forward, loss, backward, gradient all-reduce (N>1), AdamW",
+           "l2": "activations per step >> 126 MB L2 (no flush needed)"}
+    if workload == "fct" and B % CLIP_FRAMES == 0:
+        cfg["clips"] = {"frames_per_clip": CLIP_FRAMES, "clips_per_gpu": B // CLIP_FRAMES,
+                        "sharding": "one clip split by frame across the ranks" if args.strong_clips else "whole clips per rank"}
+    elif workload == "fct" and args.strong_clips:
+        cfg["clips"] = {"frames_per_clip": CLIP_FRAMES, "clips_total": args.strong_clips,
+                        "sharding": f"{args.strong_clips} clip(s) split by frame across the ranks: {B} frames per rank"}
+    return cfg
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU (default: the workload's)")
+    ap.add_argument("--clips", type=int, default=0, help="FCT: whole 16-frame clips per GPU (weak scaling; default 2 = batch 32)")
+    ap.add_argument("--strong-clips", type=int, default=0, help="FCT: this many 16-frame clips IN TOTAL, split by frame across the ranks (strong scaling)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="default workload only (no UNet / Autoencoder32K under 'extra')")
+    ap.add_argument("--torch-eager", action="store_true", help="also time the torch-eager (cuDNN/SDPA) library bar on this GPU")
+    ap.add_argument("--no-dropout", action="store_true")
+    ap.add_argument("--kernel-table", action="store_true", help="print the per-kernel time table to stderr")
+    ap.add_argument("--kernel-detail", action="store_true", help="per conv geometry rows in the kernel table")
+    ap.add_argument("--infer", action="store_true", help="eval-mode forward only (BASELINE configs[3] inference leg); "
+                    "e2e copies the whole output back to pinned host memory")
+    ap.add_argument("--no-graph", action="store_true", help="issue every kernel eagerly instead of replaying the captured step")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    key, B0, kind, cfg_name = WORKLOADS[args.workload]
+    B = args.batch or B0
+    if args.workload == "fct" and args.clips:
+        B = CLIP_FRAMES * args.clips
+    if args.workload == "fct" and args.strong_clips:
+        total = CLIP_FRAMES * args.strong_clips
+        if total % world:
+            raise SystemExit(f"--strong-clips: {total} frames do not split over {world} ranks")
+        B = total // world
+    metric, unit = "train frames/sec (fwd+bwd, 256x256)", "frames/s"
+    if args.infer:
+        metric = "inference frames/sec (eval-mode fwd, 256x256)"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        frames = CPU_FRAMES[args.workload]
+        steps, warmup = max(1, args.steps), max(1, args.warmup)
+        fps, sec, cores, kimpl = cpu_reference(args.workload, frames, steps, warmup, args.infer)
+        sample = cpu_sample_text(kimpl, frames, steps, args.infer, sec)
+        print(json.dumps({"impl": "reference", "metric": metric, "value": round(fps, 4), "unit": unit, "n_gpus": args.gpus,
+                          "steps": steps, "warmup": warmup, "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True,
+                          "scaling": "strong" if args.strong_clips else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                          "config": make_config(args, args.workload, B, world),
+                          "cpu_baseline": {"value": round(fps, 4), "unit": unit, "cores": cores, "kind": kimpl, "sample": sample},
+                          "e2e": {"value": round(fps, 4), "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch.distributed as dist
+    from hybridnet import _lib
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import datetime
+        # keep stdout to the one JSON line: NCCL writes its banner / log lines to fd 1 from C, so fd 1 is pointed
+        # at stderr for the whole run and the JSON line goes to the saved descriptor
+        sys.stdout.flush()
+        json_fd = os.dup(1)
+        os.dup2(2, 1)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        if "HN_NCCL_DEBUG" in os.environ:
+            os.environ["NCCL_DEBUG"] = os.environ["HN_NCCL_DEBUG"]
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
+    else:
+        json_fd = None
+    _lib.call("hn_check_device")
+    with_cpu = world == 1 and not args.no_cpu_baseline
+    result = run_ours(args, args.workload, B, rank, world, local, dev, args.steps, args.warmup, with_cpu, args.torch_eager)
+    is_default = (args.workload == DEFAULT_WORKLOAD and not args.batch and not args.clips and not args.strong_clips
+                  and not args.infer and not args.no_graph)
+    if world == 1 and is_default and not args.no_extra:
+        extra = {}
+        for w in EXTRA_WORKLOADS:
+            r = run_ours(args, w, WORKLOADS[w][1], rank, world, local, dev, args.steps, args.warmup, with_cpu, args.torch_eager)
+            extra[w] = {k: r[k] for k in ("value", "unit", "ms_per_step", "config", "e2e", "gpu_launches", "clocks",
+                                           "model_tensor_roofline", "roofline", "cpu_baseline", "torch_eager_b200") if k in r}
+        result["extra"] = extra
+    if rank == 0:
         if json_fd is None:
             print(json.dumps(result))
         else:
             os.write(json_fd, (json.dumps(result) + "\n").encode())
     if world > 1:
         dist.barrier()
-        # the captured graph holds NCCL's persistent plans: it must die before the communicator does,
-        # or ncclCommDestroy waits for it forever
-        del run, captured
         import gc
         gc.collect()
         torch.cuda.synchronize()
