@@ -131,11 +131,12 @@ def _conv_work(args):
 
 def _attn_work(args, bwd):
     if bwd:
-        B, N, heads, D = args[10], args[11], args[12], args[13]
+        B, N, heads, D = args[11], args[12], args[13], args[14]
     else:
         B, N, heads, D = args[5], args[6], args[7], args[8]
     f = 4.0 * B * heads * N * N * D
-    exps = float(B) * heads * N * N * (2 if bwd else 1)     # softmax exponentials (bwd recomputes P in dQ and in dK/dV)
+    # softmax exponentials: the one-pass backward (D <= 8) recomputes P once, the two-kernel form (D >= 16) twice
+    exps = float(B) * heads * N * N * ((1 if D <= 8 else 2) if bwd else 1)
     return (2.5 * f if bwd else f), 2.0 * B * N * heads * D * (8 if bwd else 4), exps
 
 

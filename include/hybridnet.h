@@ -194,8 +194,11 @@ int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpr
  * D in {4,8,16,32,64}.  Replaces nn.MultiheadAttention's core (FCT.py:37,75).   */
 int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N,
                 int heads, int D, int ldq, int ldk, int ldv, int ldo, float scale, void* stream);
+/* workspace (fp32 elements, caller-owned, uninitialised): delta [B,heads,N] and, for D <= 8, the fp32 dQ
+ * accumulator of the one-pass kernel */
+long long hn_attn_bwd_workspace(int B, int N, int heads, int D);
 int hn_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
-                const float* lse, float* delta_ws, void* dq, void* dk, void* dv, int B, int N,
+                const float* lse, float* workspace, long long workspace_floats, void* dq, void* dk, void* dv, int B, int N,
                 int heads, int D, int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk,
                 int lddv, float scale, void* stream);
 

@@ -63,7 +63,8 @@ SIGNATURES = {
                                   _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_dwconv_bwd_data_weight": [_P, _P, _P, _P, _P, _FP, _FP, _I, _I, _I, _I, _I, _I, _I, _P],
     "hn_attn_fwd": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
-    "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _P, _P, _P, _I, _I, _I, _I,
+    "hn_attn_bwd_workspace": [_I, _I, _I, _I],
+    "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _L, _P, _P, _P, _I, _I, _I, _I,
                     _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_conv_tc_supported": [POINTER(HnConv)],
     "hn_conv_tc_halo_supported": [POINTER(HnConv)],
@@ -86,7 +87,7 @@ SIGNATURES = {
     "hn_avgpool2_bwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
 }
 
-_LONG_RESULT = {"hn_conv_wgrad_tc_workspace"}
+_LONG_RESULT = {"hn_conv_wgrad_tc_workspace", "hn_attn_bwd_workspace"}
 _lib = None
 
 

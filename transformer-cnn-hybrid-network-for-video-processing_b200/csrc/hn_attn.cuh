@@ -18,6 +18,38 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// packed fp32 pairs (sm_100: one FFMA2 / FADD2 / FMUL2 issue slot for two results)
+__device__ __forceinline__ void fma2(float& d0, float& d1, float a0, float a1, float b, float c) {
+  asm("{.reg .b64 ra, rb, rc;\n"
+      "mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %4}; mov.b64 rc, {%5, %5};\n"
+      "fma.rn.ftz.f32x2 ra, ra, rb, rc;\n"
+      "mov.b64 {%0, %1}, ra;}" : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b), "f"(c));
+}
+// (a0, a1) - (c, c)
+__device__ __forceinline__ void sub2(float& d0, float& d1, float a0, float a1, float c) {
+  asm("{.reg .b64 ra, rc;\n"
+      "mov.b64 ra, {%2, %3}; mov.b64 rc, {%4, %4};\n"
+      "sub.ftz.f32x2 ra, ra, rc;\n"
+      "mov.b64 {%0, %1}, ra;}" : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(c));
+}
+__device__ __forceinline__ void mul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{.reg .b64 ra, rb;\n"
+      "mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5};\n"
+      "mul.ftz.f32x2 ra, ra, rb;\n"
+      "mov.b64 {%0, %1}, ra;}" : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1) {
+  asm("{.reg .b64 ra, rb;\n"
+      "mov.b64 ra, {%0, %1}; mov.b64 rb, {%2, %3};\n"
+      "add.ftz.f32x2 ra, ra, rb;\n"
+      "mov.b64 {%0, %1}, ra;}" : "+f"(d0), "+f"(d1) : "f"(a0), "f"(a1));
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
 template <int DP>
 __device__ __forceinline__ int tswz(int r, int c) {
   constexpr int CPR = DP / 8;
@@ -29,7 +61,9 @@ __device__ __forceinline__ int tswz(int r, int c) {
 
 // Stage rows [row0, row0+TILE) of a [N, ld] tensor (head offset already applied
 // to `base`) into a swizzled [TILE][DP] tile; rows >= N and columns >= D are zero.
-template <int D, int DP>
+// ONES (D == 4 only): column 4 of every in-range row is set to 1.0, so that P V also yields the row sum of P
+// (in fp32, from the same bf16-rounded probabilities) in output column 4 -- no FADD per score element.
+template <int D, int DP, bool ONES = false>
 __device__ __forceinline__ void stage_tile(uint8_t* tile, const bf16* base, int ld, int row0, int N, int tid, int nthreads) {
   if (D >= 8) {
     constexpr int CPR = DP / 8;
@@ -42,8 +76,9 @@ __device__ __forceinline__ void stage_tile(uint8_t* tile, const bf16* base, int 
   } else {  // D == 4: 8-byte rows, pad to 16 bytes through registers
     for (int r = tid; r < TILE; r += nthreads) {
       uint2 v = make_uint2(0u, 0u);
-      if (row0 + r < N) v = *reinterpret_cast<const uint2*>(base + (long long)(row0 + r) * ld);
-      *reinterpret_cast<uint4*>(tile + r * 16) = make_uint4(v.x, v.y, 0u, 0u);
+      const bool ok = row0 + r < N;
+      if (ok) v = *reinterpret_cast<const uint2*>(base + (long long)(row0 + r) * ld);
+      *reinterpret_cast<uint4*>(tile + r * 16) = make_uint4(v.x, v.y, (ONES && ok) ? 0x00003F80u : 0u, 0u);
     }
   }
 }

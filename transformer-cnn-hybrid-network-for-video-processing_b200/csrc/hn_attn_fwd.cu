@@ -8,7 +8,8 @@ using namespace attn;
 
 namespace {
 
-template <int D>
+// RAGGED: N is not a multiple of the 64-key tile (never the case for the FCT maps): keys past the end are masked
+template <int D, bool RAGGED>
 __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k,
                                                               const bf16* __restrict__ v, bf16* __restrict__ o,
                                                               float* __restrict__ lse, int N, int heads, int ldq, int ldk,
@@ -36,15 +37,17 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
   const float sl2 = scale * LOG2E;
   const int ntiles = (N + TILE - 1) / TILE;
 
+  // D == 4: V rows are padded to 8 channels; channel 4 carries 1.0 so that output column 4 accumulates the row sum
+  constexpr bool ONES = D == 4;
   stage_tile<D, DP>(sK[0], kb, ldk, 0, N, tid, NWARP * 32);
-  stage_tile<D, DP>(sV[0], vb, ldv, 0, N, tid, NWARP * 32);
+  stage_tile<D, DP, ONES>(sV[0], vb, ldv, 0, N, tid, NWARP * 32);
   cp_async_commit();
 
   for (int kt = 0; kt < ntiles; ++kt) {
     const int cur = kt & 1;
     if (kt + 1 < ntiles) {
       stage_tile<D, DP>(sK[cur ^ 1], kb, ldk, (kt + 1) * TILE, N, tid, NWARP * 32);
-      stage_tile<D, DP>(sV[cur ^ 1], vb, ldv, (kt + 1) * TILE, N, tid, NWARP * 32);
+      stage_tile<D, DP, ONES>(sV[cur ^ 1], vb, ldv, (kt + 1) * TILE, N, tid, NWARP * 32);
     }
     cp_async_commit();
     cp_async_wait<1>();
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
       s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
       mma_over_d<D, DP>(s[j], qa, sK[cur], j, lane);
     }
-    if ((kt + 1) * TILE > N) {   // ragged last tile: keys >= N never win
+    if (RAGGED && (kt + 1) * TILE > N) {   // ragged last tile: keys >= N never win
 #pragma unroll
       for (int j = 0; j < TILE / 8; ++j) {
         int key = kt * TILE + j * 8 + 2 * t;
@@ -67,8 +70,8 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
     float mx[2] = {mrow[0], mrow[1]};
 #pragma unroll
     for (int j = 0; j < TILE / 8; ++j) {
-      mx[0] = fmaxf(mx[0], fmaxf(s[j][0], s[j][1]));
-      mx[1] = fmaxf(mx[1], fmaxf(s[j][2], s[j][3]));
+      mx[0] = max3(mx[0], s[j][0], s[j][1]);
+      mx[1] = max3(mx[1], s[j][2], s[j][3]);
     }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -80,7 +83,7 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
     for (int h = 0; h < 2; ++h) {
       corr[h] = ex2((mrow[h] - mx[h]) * sl2);
       mrow[h] = mx[h];
-      moff[h] = mx[h] * sl2;
+      moff[h] = -mx[h] * sl2;
       lrow[h] *= corr[h];
     }
 #pragma unroll
@@ -90,12 +93,14 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
     }
 #pragma unroll
     for (int j = 0; j < TILE / 8; ++j) {
-      s[j][0] = ex2(s[j][0] * sl2 - moff[0]);
-      s[j][1] = ex2(s[j][1] * sl2 - moff[0]);
-      s[j][2] = ex2(s[j][2] * sl2 - moff[1]);
-      s[j][3] = ex2(s[j][3] * sl2 - moff[1]);
-      lrow[0] += s[j][0] + s[j][1];
-      lrow[1] += s[j][2] + s[j][3];
+      fma2(s[j][0], s[j][1], s[j][0], s[j][1], sl2, moff[0]);
+      fma2(s[j][2], s[j][3], s[j][2], s[j][3], sl2, moff[1]);
+      s[j][0] = ex2(s[j][0]); s[j][1] = ex2(s[j][1]);
+      s[j][2] = ex2(s[j][2]); s[j][3] = ex2(s[j][3]);
+      if (!ONES) {
+        add2(lrow[0], lrow[1], s[j][0], s[j][2]);
+        add2(lrow[0], lrow[1], s[j][1], s[j][3]);
+      }
     }
 #pragma unroll
     for (int kk = 0; kk < TILE / 16; ++kk) {
@@ -110,10 +115,15 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
   }
   cp_async_wait<0>();
 
+  if (ONES) {       // the row sums sit in output column 4: lane t == 2 of each row group holds them
+    lrow[0] = __shfl_sync(0xffffffffu, oacc[0][0], (lane & ~3) | 2);
+    lrow[1] = __shfl_sync(0xffffffffu, oacc[0][2], (lane & ~3) | 2);
+  } else {
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    lrow[h] += __shfl_xor_sync(0xffffffffu, lrow[h], 1);
-    lrow[h] += __shfl_xor_sync(0xffffffffu, lrow[h], 2);
+    for (int h = 0; h < 2; ++h) {
+      lrow[h] += __shfl_xor_sync(0xffffffffu, lrow[h], 1);
+      lrow[h] += __shfl_xor_sync(0xffffffffu, lrow[h], 2);
+    }
   }
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
@@ -138,9 +148,15 @@ extern "C" int hn_attn_fwd(const void* q, const void* k, const void* v, void* o,
   HN_REQUIRE(ldq % 2 == 0 && ldk % 4 == 0 && ldv % 4 == 0 && ldo % 2 == 0, "attn_fwd: bad strides");
   dim3 grid((N + NWARP * 16 - 1) / (NWARP * 16), heads, B);
   cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(DD)                                                                                              \
-  attn_fwd_kernel<DD><<<grid, NWARP * 32, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)o, lse, \
-                                                   N, heads, ldq, ldk, ldv, ldo, scale)
+#define LAUNCH(DD)                                                                                                  \
+  do {                                                                                                              \
+    if (N % TILE)                                                                                                   \
+      attn_fwd_kernel<DD, true><<<grid, NWARP * 32, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)o, \
+                                                            lse, N, heads, ldq, ldk, ldv, ldo, scale);              \
+    else                                                                                                            \
+      attn_fwd_kernel<DD, false><<<grid, NWARP * 32, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)o, \
+                                                             lse, N, heads, ldq, ldk, ldv, ldo, scale);             \
+  } while (0)
   switch (D) {
     case 4: LAUNCH(4); break;
     case 8: HN_REQUIRE(ldk % 8 == 0 && ldv % 8 == 0, "attn_fwd: D>=8 needs 16B-aligned rows"); LAUNCH(8); break;

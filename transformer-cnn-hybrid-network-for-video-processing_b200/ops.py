@@ -1033,9 +1033,10 @@ class _AttnFn(torch.autograd.Function):
         heads = ctx.heads
         N, D = H * W, C // heads
         dqkv = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=q.device)
-        delta = torch.empty((B, heads, N), dtype=torch.float32, device=q.device)
+        nws = _lib.load().hn_attn_bwd_workspace(B, N, heads, D)
+        ws = torch.empty(nws, dtype=torch.float32, device=q.device)
         call("hn_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(),
-             delta.data_ptr(), dqkv[0].data_ptr(), dqkv[1].data_ptr(), dqkv[2].data_ptr(), B, N, heads, D, ldq, ldk,
+             ws.data_ptr(), nws, dqkv[0].data_ptr(), dqkv[1].data_ptr(), dqkv[2].data_ptr(), B, N, heads, D, ldq, ldk,
              ldv, C, lddo, C, C, C, ctx.scale, _stream())
         return dqkv[0], dqkv[1], dqkv[2], None
 
