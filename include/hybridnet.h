@@ -117,6 +117,24 @@ int hn_gelu3_sum_fwd(const void* z1, const void* z2, const void* z3, void* y, lo
                      void* stream);
 int hn_gelu3_sum_bwd(const void* dy, const void* z1, const void* z2, const void* z3, void* d1,
                      void* d2, void* d3, long long n, void* stream);
+/* Wide_Focus glue fused (FCT.py:117-132, dropout 0.1 as hn_dropout's hash with the same step-counter mixing):
+ *   combine: y = sum_i dropout_i(gelu(z_i + b_i)), i=1..3 (z_i = the dilated convs run WITHOUT bias; b_i fp32 [C] or NULL)
+ *   out:     out = res + dropout(gelu(z + bias))   (res may be NULL)
+ * backward: dz_i = dy * keep_i/(1-p) * gelu'(z_i + b_i); dbias_i (fp32 [C], accumulated, may be NULL) = column sums. */
+int hn_wf_combine_fwd(const void* z1, const void* z2, const void* z3, const float* b1, const float* b2,
+                      const float* b3, void* y, long long P, int C, int ldz, int ldy, float p,
+                      unsigned long long seed1, unsigned long long seed2, unsigned long long seed3,
+                      const unsigned long long* step_counter, void* stream);
+int hn_wf_combine_bwd(const void* dy, const void* z1, const void* z2, const void* z3, const float* b1,
+                      const float* b2, const float* b3, void* d1, void* d2, void* d3, long long P, int C,
+                      int lddy, int ldz, int ldd, float p, unsigned long long seed1, unsigned long long seed2,
+                      unsigned long long seed3, const unsigned long long* step_counter, float* dbias1,
+                      float* dbias2, float* dbias3, void* stream);
+int hn_wf_out_fwd(const void* z, const float* bias, const void* res, void* out, long long P, int C, int ldz, int ldr,
+                  int ldo, float p, unsigned long long seed, const unsigned long long* step_counter, void* stream);
+int hn_wf_out_bwd(const void* dout, const void* z, const float* bias, void* dz, long long P, int C, int lddo, int ldz,
+                  int lddz, float p, unsigned long long seed, const unsigned long long* step_counter, float* dbias,
+                  void* stream);
 /* MaxPool2d(2) (FCT.py:147; UNet.py:12) forward / backward (first max wins) */
 int hn_maxpool2_fwd(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldy,
                     void* stream);
@@ -194,6 +212,8 @@ int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpr
  * D in {4,8,16,32,64}.  Replaces nn.MultiheadAttention's core (FCT.py:37,75).   */
 int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N,
                 int heads, int D, int ldq, int ldk, int ldv, int ldo, float scale, void* stream);
+/* tuning knob of the one-pass backward (D <= 8): keys per CTA, 64 or 128 (default 128); process-wide */
+int hn_attn_tune(int fused_bwd_keys_per_cta);
 /* workspace (fp32 elements, caller-owned, uninitialised): delta [B,heads,N] and, for D <= 8, the fp32 dQ
  * accumulator of the one-pass kernel */
 long long hn_attn_bwd_workspace(int B, int N, int heads, int D);

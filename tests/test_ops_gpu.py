@@ -519,3 +519,77 @@ def test_conv_transpose_tcgen05(ops):
     assert rel_l2(out, ref) < FWD_TOL
     for t, r in zip((x, w, b), want):
         assert rel_l2(t.grad, r) < BWD_TOL
+
+
+@pytest.mark.parametrize("C,p", [(8, 0.0), (16, 0.0), (64, 0.0), (8, 0.1), (32, 0.1)])
+def test_wide_focus_fused_glue(ops, C, p):
+    """hn_wf_* (csrc/hn_wide_focus.cu): sum_i dropout(gelu(z_i + b_i)) and res + dropout(gelu(z + b)) against torch
+    (p = 0), and for p > 0 the backward must re-derive exactly the forward's masks (keep scale 1/(1-p))."""
+    B, H = 2, 16
+    dev = _dev()
+    zs = [_rand(B, C, H, H, seed=10 + i).requires_grad_(True) for i in range(3)]
+    bs = [(_rand(C, seed=20 + i) * 0.3).float().requires_grad_(True) for i in range(3)]
+    res = _rand(B, C, H, H, seed=30).requires_grad_(True)
+    seeds = (11, 22, 33)
+    y = ops._WfCombineFn.apply(*[ops.to_nhwc(z) for z in zs], *bs, p, seeds)
+    out = ops._WfOutFn.apply(y, bs[0], ops.to_nhwc(res), p, 44)
+    o = ops.to_nchw(out, C)
+    gy = _rand(B, C, H, H, seed=31)
+    o.backward(gy)
+    got = [t.grad.clone() for t in (*zs, *bs, res)]
+    for t in (*zs, *bs, res):
+        t.grad = None
+    if p == 0.0:
+        yr = sum(bf16r(F.gelu(z + b.view(1, C, 1, 1))) for z, b in zip(zs, bs))
+        yr = bf16r(yr)
+        ref = res + bf16r(F.gelu(yr + bs[0].view(1, C, 1, 1)))
+        assert rel_l2(o, ref) < FWD_TOL
+        ref.backward(gy)
+        for g, t in zip(got, (*zs, *bs, res)):
+            assert rel_l2(g, t.grad) < 1.5e-2
+        return
+    # p > 0: out - res = gelu(y + b) * m with m in {0, 1/(1-p)}; backward dy = gy * m * gelu'(y + b)
+    yn = ops.to_nchw(y, C).detach()
+    act = bf16r(F.gelu(yn + bs[0].detach().view(1, C, 1, 1)))
+    ratio = (o.detach() - res.detach()) / act
+    big = act.abs() > 0.05
+    m_fwd = (ratio[big] > 0.5 / (1 - p)).float()
+    keep = float(m_fwd.mean())
+    assert abs(keep - (1 - p)) < 0.03, keep
+    kept = ratio[big][m_fwd > 0]
+    assert float((kept - 1 / (1 - p)).abs().max()) < 0.08          # bf16 rounding of out and res
+    assert torch.equal(got[-1], bf16r(gy))                          # the residual gradient passes through
+    # the three branch gradients are zero exactly where the branch was dropped; each branch keeps ~1-p
+    for gz in got[:3]:
+        frac = float((gz != 0).float().mean())
+        assert abs(frac - (1 - p) * (1 - p)) < 0.05, frac           # kept by its own mask AND by the out mask
+    # same seeds -> same masks (forward is a pure function of (seed, step counter, index))
+    y2 = ops._WfCombineFn.apply(*[ops.to_nhwc(z.detach()) for z in zs], *[b.detach() for b in bs], p, seeds)
+    assert torch.equal(y2, y.detach())
+
+
+def test_wide_focus_module_matches_unfused_reference(ops):
+    """Wide_Focus through the fused path vs the same block written with plain torch ops (dropout off)."""
+    import hybridnet
+    torch.manual_seed(0)
+    C = 16
+    m = hybridnet.FCT.__globals__["Wide_Focus"](C, C).to(_dev()).eval()
+    x = _rand(2, C, 24, 24, seed=5).requires_grad_(True)
+    out = m(x)
+    gy = _rand(2, C, 24, 24, seed=6)
+    out.backward(gy)
+    got = [x.grad.clone()] + [p.grad.clone() for p in m.parameters()]
+    x.grad = None
+    for p_ in m.parameters():
+        p_.grad = None
+    w = {k: bf16r(v.detach()).requires_grad_(True) if k.endswith("weight") else v.detach().clone().requires_grad_(True)
+         for k, v in m.state_dict().items()}
+    ys = [bf16r(F.gelu(bf16r(F.conv2d(x, w[f"conv{i}.weight"], None, 1, d, d)) + w[f"conv{i}.bias"].view(1, C, 1, 1)))
+          for i, d in ((1, 1), (2, 2), (3, 3))]
+    added = bf16r(ys[0] + ys[1] + ys[2])
+    ref = bf16r(F.gelu(bf16r(F.conv2d(added, w["conv4.weight"], None, 1, 1, 1)) + w["conv4.bias"].view(1, C, 1, 1)))
+    assert rel_l2(out, ref) < 6e-3
+    ref.backward(gy)
+    want = [x.grad] + [w[k].grad for k, _ in m.named_parameters()]
+    for g, r in zip(got, want):
+        assert rel_l2(g, r) < 2e-2

@@ -89,15 +89,9 @@ class Wide_Focus(nn.Module):
         self.dropout = nn.Dropout(0.1)
 
     def nhwc(self, x, res=None):
-        p, tr = self.dropout.p, self.training
-        if tr and p > 0.0:
-            ys = [ops.dropout(c.nhwc(x, act="gelu"), p, True) for c in (self.conv1, self.conv2, self.conv3)]
-            added = ops.add(ops.add(ys[0], ys[1]), ys[2])
-            y = ops.dropout(self.conv4.nhwc(added, act="gelu"), p, True)
-            return y if res is None else ops.add(res, y)
-        added = ops.gelu3_sum(self.conv1.nhwc(x), self.conv2.nhwc(x), self.conv3.nhwc(x))
-        y = self.conv4.nhwc(added, act="gelu")
-        return y if res is None else ops.add(res, y)
+        # the three dilated convs share one autograd node; GELU, dropout, the 3-way sum, conv4's GELU/dropout and
+        # the caller's residual add run as two fused passes each way (csrc/hn_wide_focus.cu)
+        return ops.wide_focus(x, (self.conv1, self.conv2, self.conv3, self.conv4), res, self.dropout.p, self.training)
 
     forward = _io(nhwc)
 

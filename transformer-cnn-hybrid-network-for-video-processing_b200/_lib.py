@@ -45,6 +45,11 @@ SIGNATURES = {
     "hn_add": [_P, _P, _P, _P, _L, _I, _I, _I, _I, _I, _P],
     "hn_gelu3_sum_fwd": [_P, _P, _P, _P, _L, _P],
     "hn_gelu3_sum_bwd": [_P, _P, _P, _P, _P, _P, _P, _L, _P],
+    "hn_wf_combine_fwd": [_P, _P, _P, _FP, _FP, _FP, _P, _L, _I, _I, _I, _F, c_ulonglong, c_ulonglong, c_ulonglong, _P, _P],
+    "hn_wf_combine_bwd": [_P, _P, _P, _P, _FP, _FP, _FP, _P, _P, _P, _L, _I, _I, _I, _I, _F, c_ulonglong, c_ulonglong,
+                          c_ulonglong, _P, _FP, _FP, _FP, _P],
+    "hn_wf_out_fwd": [_P, _FP, _P, _P, _L, _I, _I, _I, _I, _F, c_ulonglong, _P, _P],
+    "hn_wf_out_bwd": [_P, _P, _FP, _P, _L, _I, _I, _I, _I, _F, c_ulonglong, _P, _FP, _P],
     "hn_maxpool2_fwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
     "hn_maxpool2_bwd": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P],
     "hn_upsample2_bwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
@@ -64,6 +69,7 @@ SIGNATURES = {
     "hn_dwconv_bwd_data_weight": [_P, _P, _P, _P, _P, _FP, _FP, _I, _I, _I, _I, _I, _I, _I, _P],
     "hn_attn_fwd": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_attn_bwd_workspace": [_I, _I, _I, _I],
+    "hn_attn_tune": [_I],
     "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _L, _P, _P, _P, _I, _I, _I, _I,
                     _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_conv_tc_supported": [POINTER(HnConv)],

@@ -415,6 +415,14 @@ __global__ void attn_dq_cast_kernel(const float* __restrict__ acc, bf16* __restr
 
 }  // namespace
 
+// keys per CTA of the one-pass kernel: 128 (fewer dQ reductions) or 64 (fewer registers, more resident warps)
+static int g_fused_kb = 128;
+extern "C" int hn_attn_tune(int fused_bwd_keys_per_cta) {
+  HN_REQUIRE(fused_bwd_keys_per_cta == 64 || fused_bwd_keys_per_cta == 128, "attn_tune: keys per CTA must be 64 or 128");
+  g_fused_kb = fused_bwd_keys_per_cta;
+  return HN_OK;
+}
+
 extern "C" long long hn_attn_bwd_workspace(int B, int N, int heads, int D) {
   // delta [B, heads, N] (+ the fp32 dQ accumulator [B, N, heads*D] of the one-pass kernel for D <= 8)
   long long n = ((long long)B * heads * N + 3) / 4 * 4;
@@ -439,22 +447,27 @@ extern "C" int hn_attn_bwd(const void* q, const void* k, const void* v, const vo
   HN_CHECK_LAUNCH("attn_delta");
   if (D <= 8) {
     // one-pass kernel: P recomputed once; dQ through an fp32 accumulator
-    constexpr int KB = 128;
     const int C = heads * D;
     float* dq_acc = ws + (total + 3) / 4 * 4;
     cudaError_t e = cudaMemsetAsync(dq_acc, 0, sizeof(float) * (size_t)B * N * C, st);
     if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "attn_bwd: memset: %s", cudaGetErrorString(e));
+    const int KB = g_fused_kb;
     const int full = N / KB;                        // key blocks without a ragged edge
-#define LAUNCHF(DD, RG, GX, K0)                                                                                         \
-  attn_bwd_fused_kernel<DD, KB, RG><<<dim3(GX, heads, B), NWARP * 32, 0, st>>>(                                         \
+#define LAUNCHF(DD, KBB, RG, GX, K0)                                                                                    \
+  attn_bwd_fused_kernel<DD, KBB, RG><<<dim3(GX, heads, B), NWARP * 32, 0, st>>>(                                        \
       (const bf16*)q, (const bf16*)k, (const bf16*)v, (const bf16*)dout, lse, delta_ws, dq_acc, (bf16*)dk, (bf16*)dv, N, \
       heads, ldq, ldk, ldv, lddo, lddk, lddv, C, scale, K0)
+#define LAUNCHD(KBB, RG, GX, K0)                                                  \
+  do {                                                                            \
+    if (D == 4) LAUNCHF(4, KBB, RG, GX, K0); else LAUNCHF(8, KBB, RG, GX, K0);    \
+  } while (0)
     if (full > 0) {
-      if (D == 4) LAUNCHF(4, false, full, 0); else LAUNCHF(8, false, full, 0);
+      if (KB == 128) LAUNCHD(128, false, full, 0); else LAUNCHD(64, false, full, 0);
     }
     if (N % KB) {
-      if (D == 4) LAUNCHF(4, true, 1, full); else LAUNCHF(8, true, 1, full);
+      if (KB == 128) LAUNCHD(128, true, 1, full); else LAUNCHD(64, true, 1, full);
     }
+#undef LAUNCHD
 #undef LAUNCHF
     HN_CHECK_LAUNCH("attn_bwd_fused");
     const long long rows = (long long)B * N;

@@ -144,12 +144,11 @@ __global__ void dwln_bwd_pre_kernel(const bf16* __restrict__ x, const bf16* __re
     }
     if (ok) store8(dps + pix * ldd + c0, o);
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    atomicAdd(&sacc[c0 + j], ag[j]);
-    atomicAdd(&sacc[C + c0 + j], ab[j]);
-    atomicAdd(&sacc[2 * C + c0 + j], apb[j]);
-  }
+  // shuffle-fold the lanes that share a channel vector before touching shared memory (C = 8: all 256 threads of
+  // the CTA would otherwise contend for the same 24 words with CAS-loop float atomics)
+  col_fold8(sacc, ag, cv, CV);
+  col_fold8(sacc + C, ab, cv, CV);
+  col_fold8(sacc + 2 * C, apb, cv, CV);
   __syncthreads();
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     atomicAdd(dgamma + t * C + i, sacc[i]);

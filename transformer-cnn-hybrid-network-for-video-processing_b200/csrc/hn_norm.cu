@@ -99,11 +99,10 @@ __global__ void ln_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict
     for (int j = 0; j < 8; ++j) f[j] = rstd * (g[j] - a - f[j] * b);
     if (ok) store8(dx + pix * lddx + cv * 8, f);
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    atomicAdd(&s_acc[cv * 8 + j], pg[j]);
-    atomicAdd(&s_acc[C + cv * 8 + j], pb[j]);
-  }
+  // lanes that share a channel vector are folded by shuffles first: with C = 8 every thread of the CTA would
+  // otherwise hit the same 16 shared-memory words with CAS-loop float atomics (256-way contention)
+  col_fold8(s_acc, pg, cv, CV);
+  col_fold8(s_acc + C, pb, cv, CV);
   __syncthreads();
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     atomicAdd(dgamma + i, s_acc[i]);

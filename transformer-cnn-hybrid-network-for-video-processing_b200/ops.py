@@ -933,6 +933,143 @@ def gelu3_sum(z1, z2, z3):
     return _Gelu3SumFn.apply(z1, z2, z3)
 
 
+# ----------------------------------------------------------------------------
+# Wide_Focus (FCT.py:107-132): three dilated convs of one input, fused GELU/dropout/sum glue
+# ----------------------------------------------------------------------------
+class _MultiConvFn(torch.autograd.Function):
+    """z_i = conv(x; w_i, dilation d_i) for the three Wide_Focus branches (no bias: it is added by the glue kernel).
+    One autograd node, so that the three input gradients are summed by ONE hn_add launch instead of autograd's
+    two elementwise fan-in adds."""
+
+    @staticmethod
+    def forward(ctx, x, w1, w2, w3, dils):
+        x, _ = nhwc(x)
+        ws = (w1, w2, w3)
+        gs = [_geom(x, None, w, 1, d * (w.shape[2] - 1) // 2, d, 0, False) for w, d in zip(ws, dils)]
+        zs = [_conv_forward(g, x, None, w, None, None, ACT_NONE) for g, w in zip(gs, ws)]
+        ctx.gs = gs
+        ctx.save_for_backward(x, w1, w2, w3)
+        return tuple(zs)
+
+    @staticmethod
+    def backward(ctx, d1, d2, d3):
+        x, w1, w2, w3 = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        dxs, dws = [], []
+        for g, w, d, nw in zip(ctx.gs, (w1, w2, w3), (d1, d2, d3), need[1:4]):
+            dx, _, dw = _conv_backward(g, x, None, w, d, need[0], nw)
+            dxs.append(dx)
+            dws.append(dw)
+        dx = None
+        if need[0]:
+            a, lda = nhwc(dxs[0])
+            b, ldb = nhwc(dxs[1])
+            c, ldc = nhwc(dxs[2])
+            B, H, W, C = a.shape
+            dx = _new(B, H, W, C, a)
+            call("hn_add", a.data_ptr(), b.data_ptr(), c.data_ptr(), dx.data_ptr(), B * H * W, C, lda, ldb, ldc, C, _stream())
+        return dx, dws[0], dws[1], dws[2], None
+
+
+def _next_seed():
+    _dropout_seed[0] = (_dropout_seed[0] * 6364136223846793005 + 1442695040888963407) & ((1 << 62) - 1)
+    return _dropout_seed[0]
+
+
+def _bias_grad_target(b):
+    """fp32 [C] accumulation target for a bias gradient: the gradient sink when there is one, else scratch."""
+    sunk = _sink_for(b)
+    return (sunk, True) if sunk is not None else (_f32(b.numel(), b), False)
+
+
+class _WfCombineFn(torch.autograd.Function):
+    """y = sum_i dropout(gelu(z_i + b_i)): one pass forward, one pass backward (dz_i and the three bias gradients)."""
+
+    @staticmethod
+    def forward(ctx, z1, z2, z3, b1, b2, b3, p, seeds):
+        z1, ld = nhwc(z1)
+        z2, ld2 = nhwc(z2)
+        z3, ld3 = nhwc(z3)
+        assert ld == ld2 == ld3
+        B, H, W, C = z1.shape
+        y = _new(B, H, W, C, z1)
+        ctr = step_counter(z1.device)
+        call("hn_wf_combine_fwd", z1.data_ptr(), z2.data_ptr(), z3.data_ptr(), b1.data_ptr(), b2.data_ptr(), b3.data_ptr(),
+             y.data_ptr(), B * H * W, C, ld, C, p, seeds[0], seeds[1], seeds[2], ctr.data_ptr(), _stream())
+        ctx.p, ctx.seeds, ctx.ctr = p, seeds, ctr
+        ctx.save_for_backward(z1, z2, z3, b1, b2, b3)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        z1, z2, z3, b1, b2, b3 = ctx.saved_tensors
+        dy, lddy = nhwc(dy)
+        z1, ld = nhwc(z1)
+        B, H, W, C = z1.shape
+        d = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=z1.device)
+        tg = [_bias_grad_target(b) for b in (b1, b2, b3)]
+        call("hn_wf_combine_bwd", dy.data_ptr(), z1.data_ptr(), z2.data_ptr(), z3.data_ptr(), b1.data_ptr(), b2.data_ptr(),
+             b3.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), B * H * W, C, lddy, ld, C, ctx.p,
+             ctx.seeds[0], ctx.seeds[1], ctx.seeds[2], ctx.ctr.data_ptr(), tg[0][0].data_ptr(), tg[1][0].data_ptr(),
+             tg[2][0].data_ptr(), _stream())
+        dbs = []
+        for b, (t, sunk) in zip((b1, b2, b3), tg):
+            if sunk:
+                _sink_done(b.data_ptr())
+                dbs.append(None)
+            else:
+                dbs.append(t)
+        return d[0], d[1], d[2], dbs[0], dbs[1], dbs[2], None, None
+
+
+class _WfOutFn(torch.autograd.Function):
+    """out = res + dropout(gelu(z + bias)) (conv4 of Wide_Focus and the Transformer's second residual, FCT.py:101,131)."""
+
+    @staticmethod
+    def forward(ctx, z, bias, res, p, seed):
+        z, ld = nhwc(z)
+        B, H, W, C = z.shape
+        ldr = 0
+        if res is not None:
+            res, ldr = nhwc(res)
+        out = _new(B, H, W, C, z)
+        ctr = step_counter(z.device)
+        call("hn_wf_out_fwd", z.data_ptr(), bias.data_ptr(), _ptr(res), out.data_ptr(), B * H * W, C, ld, ldr, C, p, seed,
+             ctr.data_ptr(), _stream())
+        ctx.p, ctx.seed, ctx.ctr, ctx.has_res = p, seed, ctr, res is not None
+        ctx.save_for_backward(z, bias)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        z, bias = ctx.saved_tensors
+        dout, lddo = nhwc(dout)
+        z, ld = nhwc(z)
+        B, H, W, C = z.shape
+        dz = _new(B, H, W, C, z)
+        t, sunk = _bias_grad_target(bias)
+        call("hn_wf_out_bwd", dout.data_ptr(), z.data_ptr(), bias.data_ptr(), dz.data_ptr(), B * H * W, C, lddo, ld, C,
+             ctx.p, ctx.seed, ctx.ctr.data_ptr(), t.data_ptr(), _stream())
+        if sunk:
+            _sink_done(bias.data_ptr())
+        return dz, (None if sunk else t), (dout if ctx.has_res else None), None, None
+
+
+def wide_focus(x, convs, res, p, training):
+    """Wide_Focus.forward (FCT.py:117-132) + the residual add of Transformer.forward (FCT.py:101).
+    convs = (conv1, conv2, conv3, conv4) modules (3x3, dilation 1/2/3/1, bias)."""
+    p = float(p) if training else 0.0
+    c1, c2, c3, c4 = convs
+    if any(c.bias is None for c in convs):
+        raise RuntimeError("hybridnet wide_focus: the reference's Wide_Focus convolutions all have a bias (FCT.py:110-113)")
+    z1, z2, z3 = _MultiConvFn.apply(x, c1.weight, c2.weight, c3.weight, tuple(c.dilation[0] for c in (c1, c2, c3)))
+    seeds = (_next_seed(), _next_seed(), _next_seed(), _next_seed())
+    added = _WfCombineFn.apply(z1, z2, z3, c1.bias, c2.bias, c3.bias, p, seeds[:3])
+    z4 = _ConvFn.apply(added, None, c4.weight, None, None, 1, c4.dilation[0] * (c4.kernel_size[0] - 1) // 2, c4.dilation[0], 0,
+                       ACT_NONE, False)
+    return _WfOutFn.apply(z4, c4.bias, res, p, seeds[3])
+
+
 class _LayerNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, eps):
