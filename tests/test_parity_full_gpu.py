@@ -1,0 +1,143 @@
+"""Parity at the sizes that are actually benchmarked ("do this" item 1).
+
+* weights: the trained-weights fixture (tests/golden/trained.py: 20-60 AdamW steps of the oracle on a synthetic blob
+  dataset, recipe pinned against the unmodified reference classes) -- masks straddle 0.5 and the BatchNorm stacks are
+  no longer expanders, so the STATED tolerances apply end to end;
+* sizes: 256x256 frames for all six nets, at B=2 and at BASELINE.json's bench batches (FCT 32, UNet 32,
+  Autoencoder32K 16, Image2Image2Mask 16, latent-to-mask 16, AutoEncoder 64);
+* checker: oracle/nets.py run ON THE GPU in fp32 with TF32 off (torch ops as the checker only -- the CPU would need
+  minutes per case); train mode (batch statistics), dropout off (RNG streams cannot match);
+* stated tolerances: outputs max-abs <= 5e-2 and rel-L2 <= 2e-2, whole-gradient cosine >= 0.999 and
+  rel-L2 <= 3e-2, mask IoU at threshold 0.5 >= 0.999.  The two exceptions are named constants below with the
+  measured ideal-bf16 emulation distance that justifies them.
+"""
+import pytest
+import torch
+
+from oracle import nets
+from tests.golden import trained
+from tests.util import cosine, iou, max_abs, rel_l2
+
+pytestmark = pytest.mark.gpu
+OUT_ABS, OUT_REL, GRAD_COS, GRAD_REL, IOU = 5e-2, 2e-2, 0.999, 3e-2, 0.999
+# Autoencoder32K family, train-mode BatchNorm (37 BN layers): the oracle's OWN ideal-bf16 emulation (operands and
+# stored activations rounded to bf16, fp32 accumulation: nets.bf16_emulation) reaches only cosine 0.9875 / rel-L2
+# 0.167 (image net) and 0.998 / 0.059 (latent-to-mask) against fp32 on the trained fixture at B=2, 64x64 (measured
+# in the build container, tests/golden/trained.py header): batch-statistics gradients amplify operand rounding.
+# Bound = that distance with 2x head-room on (1 - cos); outputs keep the stated tolerance.
+AE32K_GRAD_COS, AE32K_GRAD_REL = 0.975, 0.25
+_cache = {}
+
+
+def _trained(name):
+    if name not in _cache:
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+        sd, losses = trained.train_oracle(name, device="cuda")
+        fx = torch.load(__file__.replace("test_parity_full_gpu.py", f"golden/trained_{name}.pt"))
+        # the GPU run retraces the pinned CPU trajectory over its non-chaotic part (see test_oracle_golden.py)
+        for i in range(min(10, len(losses))):
+            assert abs(losses[i] - fx["losses"][i]) <= 5e-3, (name, i, losses[i], fx["losses"][i])
+        _cache[name] = {k: v.detach().cpu() for k, v in sd.items()}
+    return _cache[name]
+
+
+def _loss(name, out, x, y):
+    return trained.loss_of(name, out, x, y)
+
+
+def _oracle_gpu(name, sd, x, y, chunk=None):
+    """fp32 oracle forward+backward on the GPU.  `chunk`: frames per pass for the nets without cross-frame coupling
+    (FCT materialises a 16384^2 score matrix per head and frame): pass 1 computes every output without a graph and
+    dL/dout of the whole-batch loss, pass 2 recomputes chunk by chunk and back-propagates that dL/dout slice."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    dev = torch.device("cuda")
+    frozen = (lambda k: k.startswith("0.")) if name == "latent2mask" else (lambda k: False)
+    params = {k: (v.to(dev).clone().requires_grad_(True) if v.is_floating_point() and "running" not in k and not frozen(k)
+                  else v.to(dev).clone()) for k, v in sd.items()}
+    xd, yd = x.to(dev), y.to(dev)
+    ctx = nets.Ctx(training=True, dropout="off")
+    if chunk is None or chunk >= x.shape[0]:
+        out = nets.FORWARDS[name](params, xd, ctx)
+        outs = out if isinstance(out, tuple) else (out,)
+        loss = _loss(name, outs, xd, yd)
+        loss.backward()
+    else:
+        with torch.no_grad():
+            parts = [nets.FORWARDS[name](params, xd[i:i + chunk], ctx) for i in range(0, x.shape[0], chunk)]
+        assert not isinstance(parts[0], tuple)
+        full = torch.cat(parts).requires_grad_(True)
+        loss = _loss(name, full, xd, yd)
+        loss.backward()
+        for i in range(0, x.shape[0], chunk):
+            o = nets.FORWARDS[name](params, xd[i:i + chunk], ctx)
+            o.backward(full.grad[i:i + chunk])
+        outs = (full.detach(),)
+    grads = {k: p.grad.detach().cpu() for k, p in params.items() if torch.is_tensor(p) and p.requires_grad and p.grad is not None}
+    return [o.detach().cpu() for o in outs], float(loss), grads
+
+
+def _product(name, sd, x, y):
+    import hybridnet
+    m = hybridnet.MODELS[name]()
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().train()
+    for mod in m.modules():
+        if isinstance(mod, (torch.nn.Dropout, torch.nn.Dropout2d)):
+            mod.p = 0.0
+    xd, yd = x.cuda(), y.cuda()
+    out = m(xd)
+    outs = out if isinstance(out, tuple) else (out,)
+    crit = hybridnet.MSELoss() if name in trained.RECONSTRUCTION else hybridnet.DiceLoss()      # the fused loss kernels
+    loss = crit(outs[-1], xd if name in trained.RECONSTRUCTION else yd)
+    loss.backward()
+    grads = {k: p.grad.detach().cpu() for k, p in m.named_parameters() if p.grad is not None}
+    return [o.detach().cpu() for o in outs], float(loss), grads
+
+
+def _check(name, B, chunk=None):
+    sd = _trained(name)
+    x, y = trained.blobs(B, 256, 4242)
+    outs, loss, grads = _product(name, sd, x, y)
+    r_outs, r_loss, r_grads = _oracle_gpu(name, sd, x, y, chunk)
+    assert set(grads) == set(r_grads), set(grads) ^ set(r_grads)
+    for o, r in zip(outs[-len(r_outs):], r_outs):
+        assert o.shape == r.shape
+        assert max_abs(o, r) <= OUT_ABS, (name, "max-abs", max_abs(o, r))
+        assert rel_l2(o, r) <= OUT_REL, (name, "rel-L2", rel_l2(o, r))
+    assert abs(loss - r_loss) <= 5e-3, (loss, r_loss)
+    ga = torch.cat([grads[k].flatten().float() for k in r_grads])
+    gb = torch.cat([r_grads[k].flatten().float() for k in r_grads])
+    gcos, grel = (AE32K_GRAD_COS, AE32K_GRAD_REL) if name in ("ae32k_image", "latent2mask") else (GRAD_COS, GRAD_REL)
+    assert cosine(ga, gb) >= gcos, (name, "grad cosine", cosine(ga, gb))
+    assert rel_l2(ga, gb) <= grel, (name, "grad rel-L2", rel_l2(ga, gb))
+    if name not in trained.RECONSTRUCTION:
+        frac = float((r_outs[-1] > 0.5).float().mean())
+        assert 0.01 < frac < 0.99, ("the trained fixture must give masks that straddle 0.5", frac)
+        assert iou(outs[-1], r_outs[-1], 0.5) >= IOU, (name, "IoU@0.5", iou(outs[-1], r_outs[-1], 0.5))
+    return grads, r_grads
+
+
+@pytest.mark.parametrize("name", ["fct", "unet", "autoencoder", "i2i2m", "ae32k_image", "latent2mask"])
+def test_256_all_models_trained_weights(name):
+    _check(name, 2)
+
+
+@pytest.mark.parametrize("name,B,chunk", [("fct", 32, 2), ("unet", 32, None), ("ae32k_image", 16, None), ("i2i2m", 16, None),
+                                          ("latent2mask", 16, None), ("autoencoder", 64, None)])
+def test_bench_batch_trained_weights(name, B, chunk):
+    """The exact batch shapes bench.py times (tile geometry with BB > 1, the halo path with W % 128 == 0, the split-K
+    weight-gradient workspace, the one-pass attention backward at N = 16384 all live here)."""
+    _check(name, B, chunk)
+
+
+def test_fct_per_tensor_gradient_cosines():
+    """Round-1 smoke() saw cosine 0.99518 on block_5.trans.conv1.weight at 64x64 with random weights: there block_5
+    works on a 2x2 map (4 tokens), each weight gradient sums only 4..8 products and bf16 rounding does not average
+    out.  At the real frame size (8x8 map) with trained weights every tensor with a non-negligible gradient must
+    reach 0.99; the whole-gradient cosine meets the stated 0.999 (checked by the tests above)."""
+    grads, r_grads = _check("fct", 2)
+    total = torch.cat([g.flatten() for g in r_grads.values()]).norm()
+    worst = min(((cosine(grads[k], r), k) for k, r in r_grads.items() if float(r.norm()) > 1e-3 * float(total)), default=(1.0, ""))
+    assert worst[0] >= 0.99, worst

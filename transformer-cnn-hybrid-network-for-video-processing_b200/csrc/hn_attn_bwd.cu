@@ -250,7 +250,7 @@ __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
 }
 
 template <int D, int KB, bool RAGGED>
-__global__ void __launch_bounds__(NWARP * 32) attn_bwd_fused_kernel(
+__global__ void __launch_bounds__(NWARP * 32, KB == 128 ? 4 : 6) attn_bwd_fused_kernel(
     const bf16* __restrict__ q, const bf16* __restrict__ k, const bf16* __restrict__ v, const bf16* __restrict__ dout,
     const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_acc, bf16* __restrict__ dk,
     bf16* __restrict__ dv, int N, int heads, int ldq, int ldk, int ldv, int lddo, int lddk, int lddv, int C, float scale, int kblock0) {

@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(TPB) augment_pack_kernel(const void* __restric
     if (U8) {
       const uint8_t* s = reinterpret_cast<const uint8_t*>(src) + ((long long)b * HW + (long long)h * W + ws) * 3;
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v[c] = (float)s[c] * (1.0f / 255.0f);      // ToTensor()
+      for (int c = 0; c < 3; ++c) v[c] = __fdiv_rn((float)s[c], 255.0f);     // ToTensor(): a true division, bit-identical to torch's .div(255)
     } else {
       const float* s = reinterpret_cast<const float*>(src) + (long long)b * 3 * HW + (long long)h * W + ws;
 #pragma unroll
