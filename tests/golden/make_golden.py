@@ -115,7 +115,7 @@ def make_trained(classes):
     from tests.golden import trained
     for name, cls in classes.items():
         model = cls()
-        model.load_state_dict(nets.init_state_dict(name, 0), strict=True)
+        model.load_state_dict(nets.init_state_dict(name, trained.INIT_SEED.get(name, 0)), strict=True)
         losses, _ = trained.train_module(model, name)
         sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
         x, _ = trained.blobs(2, trained.S, trained.EVAL_SEED)

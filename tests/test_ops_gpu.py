@@ -573,7 +573,7 @@ def test_wide_focus_module_matches_unfused_reference(ops):
     import hybridnet
     torch.manual_seed(0)
     C = 16
-    m = hybridnet.FCT.__globals__["Wide_Focus"](C, C).to(_dev()).eval()
+    m = hybridnet.Wide_Focus(C, C).to(_dev()).eval()
     x = _rand(2, C, 24, 24, seed=5).requires_grad_(True)
     out = m(x)
     gy = _rand(2, C, 24, 24, seed=6)

@@ -11,6 +11,9 @@
   rel-L2 <= 3e-2, mask IoU at threshold 0.5 >= 0.999.  The two exceptions are named constants below with the
   measured ideal-bf16 emulation distance that justifies them.
 """
+import json
+import os
+
 import pytest
 import torch
 
@@ -27,6 +30,7 @@ OUT_ABS, OUT_REL, GRAD_COS, GRAD_REL, IOU = 5e-2, 2e-2, 0.999, 3e-2, 0.999
 # Bound = that distance with 2x head-room on (1 - cos); outputs keep the stated tolerance.
 AE32K_GRAD_COS, AE32K_GRAD_REL = 0.975, 0.25
 _cache = {}
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _trained(name):
@@ -102,20 +106,31 @@ def _check(name, B, chunk=None):
     outs, loss, grads = _product(name, sd, x, y)
     r_outs, r_loss, r_grads = _oracle_gpu(name, sd, x, y, chunk)
     assert set(grads) == set(r_grads), set(grads) ^ set(r_grads)
-    for o, r in zip(outs[-len(r_outs):], r_outs):
-        assert o.shape == r.shape
-        assert max_abs(o, r) <= OUT_ABS, (name, "max-abs", max_abs(o, r))
-        assert rel_l2(o, r) <= OUT_REL, (name, "rel-L2", rel_l2(o, r))
-    assert abs(loss - r_loss) <= 5e-3, (loss, r_loss)
     ga = torch.cat([grads[k].flatten().float() for k in r_grads])
     gb = torch.cat([r_grads[k].flatten().float() for k in r_grads])
-    gcos, grel = (AE32K_GRAD_COS, AE32K_GRAD_REL) if name in ("ae32k_image", "latent2mask") else (GRAD_COS, GRAD_REL)
-    assert cosine(ga, gb) >= gcos, (name, "grad cosine", cosine(ga, gb))
-    assert rel_l2(ga, gb) <= grel, (name, "grad rel-L2", rel_l2(ga, gb))
+    m = {"model": name, "B": B, "loss": loss, "oracle_loss": r_loss,
+         "out_max_abs": max(max_abs(o, r) for o, r in zip(outs[-len(r_outs):], r_outs)),
+         "out_rel_l2": max(rel_l2(o, r) for o, r in zip(outs[-len(r_outs):], r_outs)),
+         "grad_cos": cosine(ga, gb), "grad_rel_l2": rel_l2(ga, gb), "grad_norm": float(gb.norm())}
     if name not in trained.RECONSTRUCTION:
-        frac = float((r_outs[-1] > 0.5).float().mean())
-        assert 0.01 < frac < 0.99, ("the trained fixture must give masks that straddle 0.5", frac)
-        assert iou(outs[-1], r_outs[-1], 0.5) >= IOU, (name, "IoU@0.5", iou(outs[-1], r_outs[-1], 0.5))
+        m["mask_frac_above_half"] = float((r_outs[-1] > 0.5).float().mean())
+        m["iou_at_half"] = iou(outs[-1], r_outs[-1], 0.5)
+    print("PARITY", json.dumps(m))
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "parity_metrics.jsonl"), "a") as f:
+        f.write(json.dumps(m) + "\n")
+    for o, r in zip(outs[-len(r_outs):], r_outs):
+        assert o.shape == r.shape
+    assert m["out_max_abs"] <= OUT_ABS, m
+    assert m["out_rel_l2"] <= OUT_REL, m
+    assert abs(loss - r_loss) <= 5e-3, m
+    gcos, grel = (AE32K_GRAD_COS, AE32K_GRAD_REL) if name in ("ae32k_image", "latent2mask") else (GRAD_COS, GRAD_REL)
+    assert m["grad_norm"] > 0, m
+    assert m["grad_cos"] >= gcos, m
+    assert m["grad_rel_l2"] <= grel, m
+    if name not in trained.RECONSTRUCTION:
+        assert 0.01 < m["mask_frac_above_half"] < 0.99, ("the trained fixture must give masks that straddle 0.5", m)
+        assert m["iou_at_half"] >= IOU, m
     return grads, r_grads
 
 
