@@ -45,6 +45,12 @@ int hn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int H, i
                              int Cpad, int ld, void* stream);
 int hn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int H, int W,
                              int ld, void* stream);
+/* Output head: final activation (none / ReLU / sigmoid) + NHWC bf16 -> NCHW fp32 in one pass (FCT.py:205,
+ * UNet.py:51, pyc:AE_32K L168), and its backward dz (NHWC bf16, padded channels zero) = dout * act'(out) with act'
+ * from the fp32 output (a bf16-stored saturated mask loses sigma' = y(1-y) for y > 0.998).              */
+int hn_head_fwd(const void* z, float* out, int B, int C, int H, int W, int ldz, int act, void* stream);
+int hn_head_bwd(const float* dout, const float* out, void* dz, int B, int C, int H, int W, int lddz, int act,
+                void* stream);
 /* AvgPool2d(2,2) on NHWC bf16 (FCT.py:238-240 pyramid) */
 int hn_avgpool2_fwd(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldy,
                     void* stream);
@@ -212,6 +218,9 @@ int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpr
  * D in {4,8,16,32,64}.  Replaces nn.MultiheadAttention's core (FCT.py:37,75).   */
 int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N,
                 int heads, int D, int ldq, int ldk, int ldv, int ldo, float scale, void* stream);
+/* forward, D <= 8: every poly_every-th 8-key tile computes exp2 on the FMA pipe (polynomial) instead of MUFU;
+ * 0 = never, default 4; process-wide */
+int hn_attn_tune_fwd(int poly_every);
 /* tuning knob of the one-pass backward (D <= 8): keys per CTA, 64 or 128 (default 128); process-wide */
 int hn_attn_tune(int fused_bwd_keys_per_cta);
 /* workspace (fp32 elements, caller-owned, uninitialised): delta [B,heads,N] and, for D <= 8, the fp32 dQ

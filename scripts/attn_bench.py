@@ -57,7 +57,11 @@ def run(B, N, heads, D, iters=5):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--kb", type=int, default=0)
+    ap.add_argument("--poly", type=int, default=-1)
     a = ap.parse_args()
+    if a.poly >= 0:
+        call("hn_attn_tune_fwd", a.poly)
+        print("forward polynomial share: every", a.poly, "th tile")
     if a.kb:
         call("hn_attn_tune", a.kb)
         print("fused backward keys per CTA:", a.kb)

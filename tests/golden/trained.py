@@ -25,6 +25,7 @@ STEPS = {"fct": 60, "i2i2m": 60, "unet": 20, "autoencoder": 20, "ae32k_image": 2
 # seed with all three channels alive.  Image2Image2Mask contains that AutoEncoder.
 INIT_SEED = {"autoencoder": 10, "i2i2m": 10}
 RECONSTRUCTION = ("autoencoder", "ae32k_image")
+_trained_cache = {}
 
 
 def blobs(B, S, seed, device="cpu"):
@@ -60,6 +61,15 @@ def train_oracle(name, device="cpu", steps=None):
     """The recipe through oracle/nets.py.  Returns (trained state_dict on `device`, loss trajectory)."""
     from oracle import nets
     sd = nets.init_state_dict(name, INIT_SEED.get(name, 0))
+    if name == "latent2mask":
+        # pyc:AE_32K:L232-245: the frozen encoder IS the trained image autoencoder's encoder
+        # (saved_model/EncoderDecoder_road_image2image32K.tar), not a random one
+        key = ("ae32k_image", str(device))
+        if key not in _trained_cache:
+            _trained_cache[key] = train_oracle("ae32k_image", device)[0]
+        for k, v in _trained_cache[key].items():
+            if k.startswith("encoder."):
+                sd["0." + k[len("encoder."):]] = v.detach().cpu().clone()
     frozen = (lambda k: k.startswith("0.")) if name == "latent2mask" else (lambda k: False)
     params = {k: (v.to(device).clone().requires_grad_(True)
                   if v.is_floating_point() and "running" not in k and not frozen(k) else v.to(device).clone())

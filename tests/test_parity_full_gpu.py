@@ -1,7 +1,7 @@
 """Parity at the sizes that are actually benchmarked ("do this" item 1).
 
 * weights: the trained-weights fixture (tests/golden/trained.py: 20-60 AdamW steps of the oracle on a synthetic blob
-  dataset, recipe pinned against the unmodified reference classes) -- masks straddle 0.5 and the BatchNorm stacks are
+  dataset, re-run on the CPU at test time, recipe pinned against the unmodified reference classes) -- masks straddle 0.5 and the BatchNorm stacks are
   no longer expanders, so the STATED tolerances apply end to end;
 * sizes: 256x256 frames for all six nets, at B=2 and at BASELINE.json's bench batches (FCT 32, UNet 32,
   Autoencoder32K 16, Image2Image2Mask 16, latent-to-mask 16, AutoEncoder 64);
@@ -34,14 +34,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _trained(name):
+    """The fixture weights: the recipe re-run by the oracle on the CPU with a FIXED thread count (deterministic: a
+    GPU run of the same recipe is not -- cuDNN / atomics -- and FCT's 60-step trajectory is chaotic, so every GPU run
+    would test different weights), checked against the pin made from the reference classes."""
     if name not in _cache:
-        torch.backends.cudnn.allow_tf32 = False
-        torch.backends.cuda.matmul.allow_tf32 = False
-        sd, losses = trained.train_oracle(name, device="cuda")
-        fx = torch.load(__file__.replace("test_parity_full_gpu.py", f"golden/trained_{name}.pt"))
-        # the GPU run retraces the pinned CPU trajectory over its non-chaotic part (see test_oracle_golden.py)
-        for i in range(min(10, len(losses))):
-            assert abs(losses[i] - fx["losses"][i]) <= 5e-3, (name, i, losses[i], fx["losses"][i])
+        nthreads = torch.get_num_threads()
+        torch.set_num_threads(8)
+        try:
+            sd, losses = trained.train_oracle(name, device="cpu")
+        finally:
+            torch.set_num_threads(nthreads)
+        fx = torch.load(os.path.join(ROOT, "tests", "golden", f"trained_{name}.pt"))
+        for i in range(min(20, len(losses))):
+            assert abs(losses[i] - fx["losses"][i]) <= 2e-3, (name, i, losses[i], fx["losses"][i])
         _cache[name] = {k: v.detach().cpu() for k, v in sd.items()}
     return _cache[name]
 

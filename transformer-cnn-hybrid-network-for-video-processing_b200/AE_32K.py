@@ -144,8 +144,15 @@ class Decoder_32K(nn.Module):
         act = final_act or ("sigmoid" if isinstance(self.finalactivation, nn.Sigmoid) else "relu")
         return conv_bn(self.outputDeterminerConv, self.outputDeterminerNorm, x, act=act)
 
+    def _final_act(self):
+        return "sigmoid" if isinstance(self.finalactivation, nn.Sigmoid) else "relu"
+
+    def out_nchw(self, x):
+        """NHWC latent -> NCHW fp32 output; the final activation rides the layout pass (ops.head_nchw)."""
+        return ops.head_nchw(self.nhwc(x, final_act="none"), self._out_channels, self._final_act())
+
     def forward(self, x):
-        return ops.to_nchw(self.nhwc(ops.to_nhwc(x)), self._out_channels)
+        return self.out_nchw(ops.to_nhwc(x))
 
 
 class Autoencoder32K(nn.Module):
@@ -160,7 +167,7 @@ class Autoencoder32K(nn.Module):
         return self.decoder.nhwc(self.encoder.nhwc(x))
 
     def forward(self, x):
-        return ops.to_nchw(self.nhwc(ops.to_nhwc(x)), self.decoder._out_channels)
+        return self.decoder.out_nchw(self.encoder.nhwc(ops.to_nhwc(x)))
 
 
 class LatentToMask(nn.Sequential):
@@ -179,4 +186,4 @@ class LatentToMask(nn.Sequential):
         return self[1].nhwc(self[0].nhwc(x))
 
     def forward(self, x):
-        return ops.to_nchw(self.nhwc(ops.to_nhwc(x)), 1)
+        return self[1].out_nchw(self[0].nhwc(ops.to_nhwc(x)))

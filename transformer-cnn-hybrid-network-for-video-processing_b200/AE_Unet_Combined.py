@@ -16,8 +16,8 @@ class Image2Image2Mask(nn.Module):
     def nhwc(self, x):
         latent, recon = self.image2imageAE.nhwc(x)
         # recon is [B,H,W,8] with channels 3..7 zero: exactly the padded RGB layout UNet's first conv takes
-        return latent, recon, self.unet.nhwc(recon)
+        return latent, recon, self.unet.nhwc(recon, final_act="none")
 
     def forward(self, x):
-        latent, recon, mask = self.nhwc(ops.to_nhwc(x))
-        return ops.to_nchw(latent, 128), ops.to_nchw(recon, 3), ops.to_nchw(mask, 1)
+        latent, recon, z = self.nhwc(ops.to_nhwc(x))
+        return ops.to_nchw(latent, 128), ops.to_nchw(recon, 3), ops.head_nchw(z, 1, "sigmoid")

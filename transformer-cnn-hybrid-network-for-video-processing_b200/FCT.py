@@ -241,4 +241,6 @@ class FCT(nn.Module):
         y = self.block_9.nhwc(y, x1)
         return self.ds.nhwc(y, final_act)
 
-    forward = _io(nhwc)
+    def forward(self, x):
+        # sigmoid(conv3) (FCT.py:205) + the NCHW fp32 boundary in one pass; sigma' from the fp32 mask in backward
+        return ops.head_nchw(self.nhwc(ops.to_nhwc(x), final_act="none"), 1, "sigmoid")

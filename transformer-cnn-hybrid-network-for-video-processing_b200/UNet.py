@@ -68,4 +68,5 @@ class UNet(nn.Module):
         return self.conv.nhwc(y, act=final_act)
 
     def forward(self, x):
-        return ops.to_nchw(self.nhwc(ops.to_nhwc(x)), self._out_channels)
+        # sigmoid + NHWC bf16 -> NCHW fp32 in one pass; sigma' in backward from the fp32 mask (ops.head_nchw)
+        return ops.head_nchw(self.nhwc(ops.to_nhwc(x), final_act="none"), self._out_channels, "sigmoid")

@@ -32,6 +32,8 @@ SIGNATURES = {
     "hn_nchw_f32_to_nhwc_bf16": [_FP, _P, _I, _I, _I, _I, _I, _I, _P],
     "hn_nhwc_bf16_to_nchw_f32": [_P, _FP, _I, _I, _I, _I, _I, _P],
     "hn_avgpool2_fwd": [_P, _P, _I, _I, _I, _I, _I, _I, _P],
+    "hn_head_fwd": [_P, _FP, _I, _I, _I, _I, _I, _I, _P],
+    "hn_head_bwd": [_FP, _FP, _P, _I, _I, _I, _I, _I, _I, _P],
     "hn_conv_kpad": [_I, _I, _I],
     "hn_conv_npad": [_I],
     "hn_pack_weight": [_FP, _P, _I, _I, _I, _I, _I, _L, _L, _L, _L, _L, _L, _P],
@@ -70,6 +72,7 @@ SIGNATURES = {
     "hn_attn_fwd": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_attn_bwd_workspace": [_I, _I, _I, _I],
     "hn_attn_tune": [_I],
+    "hn_attn_tune_fwd": [_I],
     "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _L, _P, _P, _P, _I, _I, _I, _I,
                     _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_conv_tc_supported": [POINTER(HnConv)],

@@ -44,6 +44,33 @@ __device__ __forceinline__ void add2(float& d0, float& d1, float a0, float a1) {
       "add.ftz.f32x2 ra, ra, rb;\n"
       "mov.b64 {%0, %1}, ra;}" : "+f"(d0), "+f"(d1) : "f"(a0), "f"(a1));
 }
+// (a0, a1) * (b0, b1) + (c, c)
+__device__ __forceinline__ void fma2v(float& d0, float& d1, float a0, float a1, float b0, float b1, float c) {
+  asm("{.reg .b64 ra, rb, rc;\n"
+      "mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; mov.b64 rc, {%6, %6};\n"
+      "fma.rn.ftz.f32x2 ra, ra, rb, rc;\n"
+      "mov.b64 {%0, %1}, ra;}" : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c));
+}
+// exp2 of two arguments <= 0 WITHOUT the exponential unit: the MUFU pipe (16 results/clk/SM) is what binds the
+// d = 4 / 8 attention, while the FMA / ALU pipes idle.  Cody-Waite split x = n + f with f in [-0.5, 0.5] (magic-number
+// rounding), degree-3 minimax 2^f (max relative error 1.0e-4, far under the bf16 rounding of the probabilities),
+// exponent added through the integer ALU.  ~5 issue slots per element in packed form against 8 MUFU clocks.
+__device__ __forceinline__ void ex2_poly2(float& p0, float& p1, float x0, float x1) {
+  const float MAGIC = 12582912.f;                 // 1.5 * 2^23: x + MAGIC rounds x to the nearest integer
+  x0 = fmaxf(x0, -125.f);
+  x1 = fmaxf(x1, -125.f);
+  float t0, t1, n0, n1, f0, f1;
+  fma2(t0, t1, x0, x1, 1.f, MAGIC);               // t = x + MAGIC
+  sub2(n0, n1, t0, t1, MAGIC);                    // n = round(x)
+  n0 = x0 - n0; n1 = x1 - n1;                     // f = x - n   (kept scalar: two independent FADDs)
+  f0 = n0; f1 = n1;
+  float q0, q1;
+  fma2(q0, q1, f0, f1, 0.05592203512787819f, 0.24264007806777954f);
+  fma2v(q0, q1, q0, q1, f0, f1, 0.6931210160255432f);
+  fma2v(q0, q1, q0, q1, f0, f1, 0.9999244809150696f);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
 __device__ __forceinline__ float max3(float a, float b, float c) {
   float d;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));

@@ -9,7 +9,8 @@ using namespace attn;
 namespace {
 
 // RAGGED: N is not a multiple of the 64-key tile (never the case for the FCT maps): keys past the end are masked
-template <int D, bool RAGGED>
+// POLY: every POLY-th 8-key tile takes its exponentials from the FMA-pipe polynomial instead of MUFU (0 = never)
+template <int D, bool RAGGED, int POLY>
 __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k,
                                                               const bf16* __restrict__ v, bf16* __restrict__ o,
                                                               float* __restrict__ lse, int N, int heads, int ldq, int ldk,
@@ -95,8 +96,13 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
     for (int j = 0; j < TILE / 8; ++j) {
       fma2(s[j][0], s[j][1], s[j][0], s[j][1], sl2, moff[0]);
       fma2(s[j][2], s[j][3], s[j][2], s[j][3], sl2, moff[1]);
-      s[j][0] = ex2(s[j][0]); s[j][1] = ex2(s[j][1]);
-      s[j][2] = ex2(s[j][2]); s[j][3] = ex2(s[j][3]);
+      if (POLY > 0 && (j % (POLY > 0 ? POLY : 1)) == (POLY > 0 ? POLY : 1) - 1) {
+        ex2_poly2(s[j][0], s[j][1], s[j][0], s[j][1]);
+        ex2_poly2(s[j][2], s[j][3], s[j][2], s[j][3]);
+      } else {
+        s[j][0] = ex2(s[j][0]); s[j][1] = ex2(s[j][1]);
+        s[j][2] = ex2(s[j][2]); s[j][3] = ex2(s[j][3]);
+      }
       if (!ONES) {
         add2(lrow[0], lrow[1], s[j][0], s[j][2]);
         add2(lrow[0], lrow[1], s[j][1], s[j][3]);
@@ -142,20 +148,32 @@ __global__ void __launch_bounds__(NWARP * 32) attn_fwd_kernel(const bf16* __rest
 
 }  // namespace
 
+static int g_fwd_poly = 4;
+extern "C" int hn_attn_tune_fwd(int poly_every) {
+  HN_REQUIRE(poly_every == 0 || poly_every == 2 || poly_every == 3 || poly_every == 4 || poly_every == 8, "attn_tune_fwd: 0, 2, 3, 4 or 8");
+  g_fwd_poly = poly_every;
+  return HN_OK;
+}
+
 extern "C" int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N, int heads,
                            int D, int ldq, int ldk, int ldv, int ldo, float scale, void* stream) {
   HN_REQUIRE(q && k && v && o && lse && B > 0 && N > 0 && heads > 0, "attn_fwd: bad args");
   HN_REQUIRE(ldq % 2 == 0 && ldk % 4 == 0 && ldv % 4 == 0 && ldo % 2 == 0, "attn_fwd: bad strides");
   dim3 grid((N + NWARP * 16 - 1) / (NWARP * 16), heads, B);
   cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(DD)                                                                                                  \
-  do {                                                                                                              \
-    if (N % TILE)                                                                                                   \
-      attn_fwd_kernel<DD, true><<<grid, NWARP * 32, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)o, \
-                                                            lse, N, heads, ldq, ldk, ldv, ldo, scale);              \
-    else                                                                                                            \
-      attn_fwd_kernel<DD, false><<<grid, NWARP * 32, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)o, \
-                                                             lse, N, heads, ldq, ldk, ldv, ldo, scale);             \
+#define LAUNCH_P(DD, RG, PL)                                                                                        \
+  attn_fwd_kernel<DD, RG, PL><<<grid, NWARP * 32, 0, st>>>((const bf16*)q, (const bf16*)k, (const bf16*)v, (bf16*)o, lse, \
+                                                         N, heads, ldq, ldk, ldv, ldo, scale)
+// head dims 4 / 8 are bound by the exponential unit: a share of the tiles goes to the polynomial (g_fwd_poly, default 4
+// = every 4th tile); the larger head dims are tensor-bound and keep MUFU
+#define LAUNCH(DD)                                                              \
+  do {                                                                          \
+    if (N % TILE) LAUNCH_P(DD, true, 0);                                        \
+    else if (DD > 8 || g_fwd_poly == 0) LAUNCH_P(DD, false, 0);                 \
+    else if (g_fwd_poly == 2) LAUNCH_P(DD, false, 2);                           \
+    else if (g_fwd_poly == 3) LAUNCH_P(DD, false, 3);                           \
+    else if (g_fwd_poly == 8) LAUNCH_P(DD, false, 8);                           \
+    else LAUNCH_P(DD, false, 4);                                                \
   } while (0)
   switch (D) {
     case 4: LAUNCH(4); break;

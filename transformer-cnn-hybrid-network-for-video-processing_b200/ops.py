@@ -185,6 +185,35 @@ def to_nchw(x, C):
     return _ToNCHW.apply(x, C)
 
 
+class _HeadFn(torch.autograd.Function):
+    """NCHW fp32 output = act(z) from the NHWC bf16 pre-activation: final activation + layout boundary in one pass;
+    backward takes act' from the fp32 output (exact sigma' even where the mask saturates)."""
+
+    @staticmethod
+    def forward(ctx, z, C, act):
+        z, ld = nhwc(z)
+        B, H, W, Cp = z.shape
+        out = torch.empty((B, C, H, W), dtype=torch.float32, device=z.device)
+        call("hn_head_fwd", z.data_ptr(), out.data_ptr(), B, C, H, W, ld, act, _stream())
+        ctx.act, ctx.Cp = act, Cp
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (out,) = ctx.saved_tensors
+        dout = dout.contiguous().float()
+        B, C, H, W = out.shape
+        dz = _new(B, H, W, ctx.Cp, out)
+        call("hn_head_bwd", dout.data_ptr(), out.data_ptr(), dz.data_ptr(), B, C, H, W, ctx.Cp, ctx.act, _stream())
+        return dz, None, None
+
+
+def head_nchw(z, C, act="sigmoid"):
+    """act(z) as the module's NCHW fp32 output (FCT.py:205, UNet.py:51, pyc:AE_32K L168)."""
+    return _HeadFn.apply(z, C, ACTS[act])
+
+
 class _AvgPool2Fn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):
