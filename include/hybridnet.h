@@ -218,6 +218,13 @@ int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpr
  * D in {4,8,16,32,64}.  Replaces nn.MultiheadAttention's core (FCT.py:37,75).   */
 int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N,
                 int heads, int D, int ldq, int ldk, int ldv, int ldo, float scale, void* stream);
+/* tcgen05 / TMEM / TMA form of hn_attn_fwd for the exponential-bound shapes: D in {4, 8}, two heads, N %% 128 == 0,
+ * 16-byte aligned rows.  K / V tiles arrive as TMA boxes, S = Q K^T and O += P [V | 1] run on tcgen05.mma (S, P and O
+ * live in TMEM; the ones panel makes the tensor core deliver the softmax row sum), the softmax warps read S with
+ * tcgen05.ld.  poly_every in {0, 2, 3, 4}: share of the exponentials taken on the FMA pipe.             */
+int hn_attn_fwd_tc_supported(int N, int D, int ldq, int ldk, int ldv, int ldo);
+int hn_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N, int heads, int D,
+                   int ldq, int ldk, int ldv, int ldo, float scale, int poly_every, void* stream);
 /* forward, D <= 8: every poly_every-th 8-key tile computes exp2 on the FMA pipe (polynomial) instead of MUFU;
  * 0 = never, default 4; process-wide */
 int hn_attn_tune_fwd(int poly_every);

@@ -14,6 +14,9 @@ from hybridnet._lib import call  # noqa: E402
 MUFU = 4.647e12
 
 
+TC = {"on": False, "poly": 0}
+
+
 def run(B, N, heads, D, iters=5):
     C = heads * D
     dev = torch.device("cuda")
@@ -28,6 +31,10 @@ def run(B, N, heads, D, iters=5):
     scale = 1.0 / math.sqrt(D)
 
     def fwd():
+        if TC["on"] and _lib.load().hn_attn_fwd_tc_supported(N, D, C, C, C, C):
+            call("hn_attn_fwd_tc", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D, C, C, C, C,
+                 scale, TC["poly"], st)
+            return
         call("hn_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D, C, C, C, C, scale, st)
 
     def bwd():
@@ -58,7 +65,11 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--kb", type=int, default=0)
     ap.add_argument("--poly", type=int, default=-1)
+    ap.add_argument("--tc", type=int, default=-1, help="tcgen05 forward with this polynomial share (0, 2, 3, 4)")
     a = ap.parse_args()
+    if a.tc >= 0:
+        TC["on"], TC["poly"] = True, a.tc
+        print("tcgen05 forward, polynomial share: every", a.tc)
     if a.poly >= 0:
         call("hn_attn_tune_fwd", a.poly)
         print("forward polynomial share: every", a.poly, "th tile")

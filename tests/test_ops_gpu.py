@@ -367,9 +367,21 @@ def test_dwconv_relu_ln_qkv(ops, C):
         assert rel_l2(t.grad, r) < 1.5e-2
 
 
-@pytest.mark.parametrize("D,N", [(4, 256), (4, 100), (8, 256), (16, 192), (32, 64), (64, 64), (64, 4), (8, 1024)])
-def test_flash_attention(ops, D, N):
-    """softmax(QK^T/sqrt(d))V, heads=2, incl. ragged N (not a multiple of the 64-token tile)."""
+@pytest.mark.parametrize("D,N,tc", [(4, 256, 0), (4, 100, 0), (8, 256, 0), (16, 192, 0), (32, 64, 0), (64, 64, 0), (64, 4, 0),
+                                    (8, 1024, 0), (4, 128, 1), (4, 256, 1), (8, 256, 1), (4, 1024, 1), (8, 1024, 2), (4, 2048, 3)])
+def test_flash_attention(ops, D, N, tc):
+    """softmax(QK^T/sqrt(d))V, heads=2, incl. ragged N (not a multiple of the 64-token tile).
+    tc > 0: the tcgen05 / TMEM / TMA forward (hn_attn_fwd_tc); tc = 2, 3: with every 2nd / 3rd exponential pair on the
+    FMA-pipe polynomial."""
+    if tc:
+        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = True, (0 if tc == 1 else tc)
+    try:
+        _flash_attention_case(ops, D, N)
+    finally:
+        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = False, 0
+
+
+def _flash_attention_case(ops, D, N):
     B, heads = 2, 2
     C = heads * D
     q, k, v = [_rand(B, N, C, seed=s, scale=1.5).requires_grad_(True) for s in (1, 2, 3)]

@@ -72,6 +72,8 @@ SIGNATURES = {
     "hn_attn_fwd": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "hn_attn_bwd_workspace": [_I, _I, _I, _I],
     "hn_attn_tune": [_I],
+    "hn_attn_fwd_tc_supported": [_I, _I, _I, _I, _I, _I],
+    "hn_attn_fwd_tc": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _I, _P],
     "hn_attn_tune_fwd": [_I],
     "hn_attn_bwd": [_P, _P, _P, _P, _P, _FP, _FP, _L, _P, _P, _P, _I, _I, _I, _I,
                     _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],

@@ -1169,6 +1169,10 @@ def dwconv_relu_ln_qkv(x, w, b, gamma, beta, eps=1e-5):
     return _DwLnQKVFn.apply(x, w, b, gamma, beta, eps)
 
 
+ATTN_FWD_TC = False          # tcgen05 / TMEM / TMA attention forward for D in {4, 8}, N % 128 == 0 (hn_attn_fwd_tc)
+ATTN_FWD_TC_POLY = 0         # share of its exponentials on the FMA pipe: every n-th pair (0 = none)
+
+
 class _AttnFn(torch.autograd.Function):
     """softmax(Q K^T / sqrt(d)) V per head, flash style; q,k,v: [B,H,W,heads*d] (N = H*W tokens)."""
 
@@ -1182,8 +1186,12 @@ class _AttnFn(torch.autograd.Function):
         scale = 1.0 / math.sqrt(D)
         o = _new(B, H, W, C, q)
         lse = torch.empty((B, heads, N), dtype=torch.float32, device=q.device)
-        call("hn_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D,
-             ldq, ldk, ldv, C, scale, _stream())
+        if ATTN_FWD_TC and heads == 2 and _lib.load().hn_attn_fwd_tc_supported(N, D, ldq, ldk, ldv, C):
+            call("hn_attn_fwd_tc", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D,
+                 ldq, ldk, ldv, C, scale, ATTN_FWD_TC_POLY, _stream())
+        else:
+            call("hn_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D,
+                 ldq, ldk, ldv, C, scale, _stream())
         ctx.heads, ctx.scale = heads, scale
         ctx.save_for_backward(q, k, v, o, lse)
         return o
