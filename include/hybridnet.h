@@ -225,6 +225,15 @@ int hn_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse
 int hn_attn_fwd_tc_supported(int N, int D, int ldq, int ldk, int ldv, int ldo);
 int hn_attn_fwd_tc(const void* q, const void* k, const void* v, void* o, float* lse, int B, int N, int heads, int D,
                    int ldq, int ldk, int ldv, int ldo, float scale, int poly_every, void* stream);
+/* tcgen05 / TMEM / TMA one-pass backward for the same shapes (csrc/hn_attn_tc.cu): CTA = 128 keys, dK / dV accumulate in
+ * TMEM, the per-query lse / delta terms ride the idle upper half of the K = 16 contraction as three-term bf16 splits, dQ
+ * leaves through an fp32 accumulator.  workspace (fp32 elements) = hn_attn_bwd_tc_workspace().             */
+long long hn_attn_bwd_tc_workspace(int B, int N, int heads, int D);
+int hn_attn_bwd_tc_supported(int N, int D, int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk, int lddv);
+int hn_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
+                   float* workspace, long long workspace_floats, void* dq, void* dk, void* dv, int B, int N, int heads,
+                   int D, int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk, int lddv, float scale,
+                   int poly_every, void* stream);
 /* forward, D <= 8: every poly_every-th 8-key tile computes exp2 on the FMA pipe (polynomial) instead of MUFU;
  * 0 = never, default 4; process-wide */
 int hn_attn_tune_fwd(int poly_every);

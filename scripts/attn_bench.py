@@ -14,7 +14,7 @@ from hybridnet._lib import call  # noqa: E402
 MUFU = 4.647e12
 
 
-TC = {"on": False, "poly": 0}
+TC = {"on": False, "poly": 0, "bwd": False}
 
 
 def run(B, N, heads, D, iters=5):
@@ -37,7 +37,14 @@ def run(B, N, heads, D, iters=5):
             return
         call("hn_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D, C, C, C, C, scale, st)
 
+    nws_tc = _lib.load().hn_attn_bwd_tc_workspace(B, N, heads, D)
+    ws_tc = torch.empty(nws_tc, dtype=torch.float32, device=dev)
+
     def bwd():
+        if TC["bwd"] and _lib.load().hn_attn_bwd_tc_supported(N, D, C, C, C, C, C, C, C, C):
+            call("hn_attn_bwd_tc", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(), ws_tc.data_ptr(), nws_tc,
+                 dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, N, heads, D, C, C, C, C, C, C, C, C, scale, TC["poly"], st)
+            return
         call("hn_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(), ws.data_ptr(), nws,
              dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, N, heads, D, C, C, C, C, C, C, C, C, scale, st)
     res = {}
@@ -66,9 +73,11 @@ if __name__ == "__main__":
     ap.add_argument("--kb", type=int, default=0)
     ap.add_argument("--poly", type=int, default=-1)
     ap.add_argument("--tc", type=int, default=-1, help="tcgen05 forward with this polynomial share (0, 2, 3, 4)")
+    ap.add_argument("--tcbwd", action="store_true", help="tcgen05 backward as well (with --tc)")
     a = ap.parse_args()
+    ap.add_argument  # noqa
     if a.tc >= 0:
-        TC["on"], TC["poly"] = True, a.tc
+        TC["on"], TC["poly"], TC["bwd"] = True, a.tc, a.tcbwd
         print("tcgen05 forward, polynomial share: every", a.tc)
     if a.poly >= 0:
         call("hn_attn_tune_fwd", a.poly)

@@ -24,7 +24,11 @@ tot = sum(float((grads[k].float() - r).norm() ** 2) for k, r in r_grads.items())
 tot_e = sum(float((e_grads[k].float() - r).norm() ** 2) for k, r in r_grads.items())
 gn = sum(float(r.norm() ** 2) for r in r_grads.values())
 print(f"{name} B={B}: product rel {(tot / gn) ** 0.5:.4f}   emulation rel {(tot_e / gn) ** 0.5:.4f}")
-print(f"outputs: product rel {rel_l2(outs[-1], r_outs[-1]):.5f}  emulation rel {rel_l2(e_outs[-1], r_outs[-1]):.5f}")
+print(f"outputs: product rel {rel_l2(outs[-1], r_outs[-1]):.5f}  emulation rel {rel_l2(e_outs[-1], r_outs[-1]):.5f}   "
+      f"product max-abs {float((outs[-1] - r_outs[-1]).abs().max()):.4f}  emulation max-abs {float((e_outs[-1] - r_outs[-1]).abs().max()):.4f}")
+ga = torch.cat([grads[k].flatten().float() for k in r_grads]); gb = torch.cat([r_grads[k].flatten().float() for k in r_grads])
+ge = torch.cat([e_grads[k].flatten().float() for k in r_grads])
+print(f"whole gradient: product cos {cosine(ga, gb):.5f} rel {rel_l2(ga, gb):.4f}   emulation cos {cosine(ge, gb):.5f} rel {rel_l2(ge, gb):.4f}")
 rows = []
 for k, r in r_grads.items():
     d = float((grads[k].float() - r).norm() ** 2)

@@ -129,7 +129,7 @@ def test_repack_all_refreshes_every_packed_weight(ops):
     input-gradient, stride-2 input-gradient and transposed-conv layouts) after an in-place weight update."""
     import contextlib
     from hybridnet import _lib
-    ops.invalidate_packed()
+    ops.clear_packed()
     x = _rand(2, 64, 16, 16, seed=21).requires_grad_(True)
     w3 = _rand(64, 64, 3, 3, seed=22, scale=0.05).requires_grad_(True)       # stride 1: fwd + dgradf
     w2 = _rand(128, 64, 3, 3, seed=23, scale=0.05).requires_grad_(True)      # stride 2: fwd + s2dgrad
@@ -368,17 +368,20 @@ def test_dwconv_relu_ln_qkv(ops, C):
 
 
 @pytest.mark.parametrize("D,N,tc", [(4, 256, 0), (4, 100, 0), (8, 256, 0), (16, 192, 0), (32, 64, 0), (64, 64, 0), (64, 4, 0),
-                                    (8, 1024, 0), (4, 128, 1), (4, 256, 1), (8, 256, 1), (4, 1024, 1), (8, 1024, 2), (4, 2048, 3)])
+                                    (8, 1024, 0), (4, 128, 1), (4, 256, 1), (8, 256, 1), (4, 1024, 1), (8, 1024, 2), (4, 2048, 3),
+                                    (4, 128, 11), (4, 256, 11), (8, 256, 11), (4, 1024, 11), (8, 1024, 12), (4, 2048, 13)])
 def test_flash_attention(ops, D, N, tc):
     """softmax(QK^T/sqrt(d))V, heads=2, incl. ragged N (not a multiple of the 64-token tile).
     tc > 0: the tcgen05 / TMEM / TMA forward (hn_attn_fwd_tc); tc = 2, 3: with every 2nd / 3rd exponential pair on the
     FMA-pipe polynomial."""
-    if tc:
-        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = True, (0 if tc == 1 else tc)
+    if tc:                        # tc >= 10: the tcgen05 backward (hn_attn_bwd_tc) as well
+        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = True, (0 if tc % 10 == 1 else tc % 10)
+        ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY = tc >= 10, (0 if tc % 10 == 1 else tc % 10)
     try:
         _flash_attention_case(ops, D, N)
     finally:
         ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = False, 0
+        ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY = False, 0
 
 
 def _flash_attention_case(ops, D, N):

@@ -315,8 +315,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
       *reinterpret_cast<uint4*>(op) = w;
     } else {
       uint2 w;
-      w.x = pack_bf16(__uint_as_float(ov[4 * head]) * inv, __uint_as_float(ov[4 * head + 1]) * inv);
-      w.y = pack_bf16(__uint_as_float(ov[4 * head + 2]) * inv, __uint_as_float(ov[4 * head + 3]) * inv);
+      w.x = pack_bf16(__uint_as_float(head ? ov[4] : ov[0]) * inv, __uint_as_float(head ? ov[5] : ov[1]) * inv);
+      w.y = pack_bf16(__uint_as_float(head ? ov[6] : ov[2]) * inv, __uint_as_float(head ? ov[7] : ov[3]) * inv);
       *reinterpret_cast<uint2*>(op) = w;
     }
     lse[((long long)b * heads + head) * N + q0 + row] = m_ref * scale + logf(l);
@@ -326,6 +326,289 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+// =====================================================================================================================
+// One-pass backward on tcgen05 / TMEM / TMA (D = 4, 8; N % 128 == 0).
+//
+//   CTA   = 128 keys of one (batch, head) = the TMEM lanes; K, V staged once (masked to this head for D = 4);
+//           dK, dV accumulate in TMEM over the whole query sweep; 2 CTAs per SM (256 TMEM columns each)
+//   warp 0  TMA producer: per 64-query tile four {8 ch, 64 rows} boxes: Q, dO and two auxiliary panels (below)
+//   warp 1  MMA issuer.  Per tile, with P^T / dS^T written by the softmax warps in between:
+//             S'^T [128 keys, 64 q] = [K | E] x [Q  | auxL]^T     (K = 16: 8 channels + 3 ones x 3 split terms)
+//             dP'^T[128 keys, 64 q] = [V | E] x [dO | auxD]^T
+//             dV [128 keys, 16] += P^T  (TMEM) x dO (smem, MN-major)        4 x K = 16
+//             dK [128 keys, 16] += dS^T (TMEM) x Q  (smem, MN-major)        4 x K = 16
+//             dQ [ 64 q,   16]  = dS (smem, MN-major A, M = 64) x K (smem, MN-major)   8 x K = 16
+//   warps 2-5  one thread per key row: tcgen05.ld S'^T, dP'^T -> P = exp2(S' c), dS = P dP' -> bf16 pairs -> tcgen05.st
+//           (over the columns just consumed) and st.shared (dS in the M-major layout the dQ product reads); then they
+//           drain the previous tile's dQ from TMEM into the fp32 accumulator with vector reductions.
+//   The per-QUERY terms live on the COLUMNS here, so they cannot be per-thread scalars as in the forward.  They ride the
+//   idle upper half of the K = 16 contraction instead: auxL row = -lse/scale split into three bf16 terms (hi, mid, lo:
+//   2^-24 relative), auxD row = -delta likewise, against three ones in the stationary operand (panel E), so
+//   S' = q.k - lse/scale and dP' = dO.v - delta come out of the tensor core and the softmax warps need no per-column
+//   operand at all: 2 MUFU + 2 FMUL2 + 2 F2FP per pair of score elements.
+constexpr int TQB = 64;                       // queries per tile (columns)
+constexpr int QPANEL = TQB * 16;              // one {8 ch, 64 rows} box
+constexpr int NSTB = 4;
+constexpr int DSBUF = (TQB / 8) * PANEL;      // dS tile, M-major: 8 query blocks x [128 key rows x 16 B]
+constexpr int B_OFF_KM = 0, B_OFF_VM = PANEL, B_OFF_ST = 2 * PANEL;
+constexpr int B_OFF_DS = B_OFF_ST + NSTB * 4 * QPANEL;
+constexpr int B_OFF_E = B_OFF_DS + 2 * DSBUF;
+constexpr int B_OFF_Z = B_OFF_E + PANEL;
+constexpr int B_SMEM = B_OFF_Z + PANEL;
+constexpr int C_ST = 0, C_DPT = 64, C_DV = 128, C_DK = 144, C_DQ = 160;     // TMEM columns
+constexpr uint32_t IDESC_BS = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TQB >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+constexpr uint32_t IDESC_BKV = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(16 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+constexpr uint32_t IDESC_BQ = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(16 >> 3) << 17) | ((uint32_t)(TQB >> 4) << 24);
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// delta = rowsum(dO o O) per (b, head, n) and the two auxiliary panels: 16-byte rows {hi, mid, lo, 0, 0, 0, 0, 0} of
+// -lse/scale and of -delta (three-term bf16 splits)
+__device__ __forceinline__ uint2 split3(float v) {
+  const bf16 h = __float2bfloat16(v);
+  const float r1 = v - __bfloat162float(h);
+  const bf16 m = __float2bfloat16(r1);
+  const bf16 l = __float2bfloat16(r1 - __bfloat162float(m));
+  uint2 w;
+  w.x = (uint32_t)__bfloat16_as_ushort(h) | ((uint32_t)__bfloat16_as_ushort(m) << 16);
+  w.y = (uint32_t)__bfloat16_as_ushort(l);
+  return w;
+}
+__global__ void attn_bwd_prep_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dout, const float* __restrict__ lse,
+                                     uint4* __restrict__ auxL, uint4* __restrict__ auxD, int N, int heads, int D, int ldo,
+                                     int lddo, float inv_scale, long long total) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int n = (int)(i % N);
+  const long long r = i / N;
+  const int head = (int)(r % heads);
+  const long long b = r / heads;
+  const bf16* po = o + (b * N + n) * ldo + head * D;
+  const bf16* pd = dout + (b * N + n) * lddo + head * D;
+  float s = 0.f;
+  for (int j = 0; j < D; j += 2) {
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const bf162*>(po + j));
+    const float2 c = __bfloat1622float2(*reinterpret_cast<const bf162*>(pd + j));
+    s += a.x * c.x + a.y * c.y;
+  }
+  const uint2 l3 = split3(-lse[i] * inv_scale), d3 = split3(-s);
+  auxL[i] = make_uint4(l3.x, l3.y, 0u, 0u);
+  auxD[i] = make_uint4(d3.x, d3.y, 0u, 0u);
+}
+
+template <int D, int POLY>
+__global__ void __launch_bounds__(TC_THREADS, 2)
+attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_constant__ CUtensorMap mapDO,
+                   const __grid_constant__ CUtensorMap mapL, const __grid_constant__ CUtensorMap mapD,
+                   const bf16* __restrict__ k, const bf16* __restrict__ v, float* __restrict__ dq_acc, bf16* __restrict__ dk,
+                   bf16* __restrict__ dv, int N, int heads, int ldk, int ldv, int lddk, int lddv, int C, float scale) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bars[2 * NSTB + 4];
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int head = blockIdx.y, b = blockIdx.z;
+  const int k0 = blockIdx.x * 128;
+  const int ntiles = N / TQB;
+  // rotate the query sweep per CTA: the CTAs of one (batch, head) reduce into different dQ rows at any moment
+  const int rot = (int)(((long long)blockIdx.x * 37) % ntiles);
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t q_full = smem_u32(&bars[0]), q_empty = smem_u32(&bars[NSTB]);
+  const uint32_t s_full = smem_u32(&bars[2 * NSTB]), p_full = smem_u32(&bars[2 * NSTB + 1]);
+  const uint32_t dq_full = smem_u32(&bars[2 * NSTB + 2]);          // two barriers: dQ buffer 0 / 1
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NSTB; ++s) { mbar_init(q_full + 8 * s, 1); mbar_init(q_empty + 8 * s, 1); }
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 4);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_full + 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp >= 2) {
+    const int row = threadIdx.x - 64;
+    uint4 kv, vv;
+    if (D == 8) {
+      kv = *reinterpret_cast<const uint4*>(k + ((long long)b * N + k0 + row) * ldk + head * 8);
+      vv = *reinterpret_cast<const uint4*>(v + ((long long)b * N + k0 + row) * ldv + head * 8);
+    } else {
+      kv = *reinterpret_cast<const uint4*>(k + ((long long)b * N + k0 + row) * ldk);
+      vv = *reinterpret_cast<const uint4*>(v + ((long long)b * N + k0 + row) * ldv);
+      if (head == 0) { kv.z = kv.w = 0u; vv.z = vv.w = 0u; } else { kv.x = kv.y = 0u; vv.x = vv.y = 0u; }
+    }
+    *reinterpret_cast<uint4*>(smem + B_OFF_KM + row * 16) = kv;
+    *reinterpret_cast<uint4*>(smem + B_OFF_VM + row * 16) = vv;
+    *reinterpret_cast<uint4*>(smem + B_OFF_E + row * 16) = make_uint4(0x3F803F80u, 0x00003F80u, 0u, 0u);   // {1, 1, 1, 0, ...}
+    *reinterpret_cast<uint4*>(smem + B_OFF_Z + row * 16) = make_uint4(0u, 0u, 0u, 0u);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapQ) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapDO) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapL) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapD) : "memory");
+      const int c0 = D == 8 ? head * 8 : 0;
+      for (int j = 0; j < ntiles; ++j) {
+        const int st = j % NSTB;
+        int jt = j + rot; if (jt >= ntiles) jt -= ntiles;
+        mbar_wait(q_empty + 8 * st, ((j / NSTB) & 1) ^ 1);
+        mbar_arrive_expect_tx(q_full + 8 * st, 4 * QPANEL);
+        const uint32_t dst = sbase + B_OFF_ST + st * 4 * QPANEL;
+        const int row = b * N + jt * TQB, arow = (b * heads + head) * N + jt * TQB;
+        tma_load_2d(dst, &mapQ, q_full + 8 * st, c0, row);
+        tma_load_2d(dst + QPANEL, &mapL, q_full + 8 * st, 0, arow);
+        tma_load_2d(dst + 2 * QPANEL, &mapDO, q_full + 8 * st, c0, row);
+        tma_load_2d(dst + 3 * QPANEL, &mapD, q_full + 8 * st, 0, arow);
+      }
+    }
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    const uint32_t km = sbase + B_OFF_KM, vm = sbase + B_OFF_VM, ep = sbase + B_OFF_E, zp = sbase + B_OFF_Z;
+    const uint64_t a_k = make_desc_nosw(km, ep - km, 128), a_v = make_desc_nosw(vm, ep - vm, 128);
+    for (int j = 0; j < ntiles; ++j) {
+      const int st = j % NSTB;
+      const uint32_t qp = sbase + B_OFF_ST + st * 4 * QPANEL, dop = qp + 2 * QPANEL;
+      const uint32_t dsb = sbase + B_OFF_DS + (j & 1) * DSBUF;
+      mbar_wait(q_full + 8 * st, (j / NSTB) & 1);
+      tc_fence_after();
+      if (leader) {
+        umma_ss(tmem + C_ST, a_k, make_desc_nosw(qp, QPANEL, 128), IDESC_BS, 0u);
+        umma_ss(tmem + C_DPT, a_v, make_desc_nosw(dop, QPANEL, 128), IDESC_BS, 0u);
+        umma_commit(s_full);
+      }
+      __syncwarp();
+      mbar_wait(p_full, j & 1);
+      tc_fence_after();
+      if (leader) {
+#pragma unroll
+        for (int ks = 0; ks < TQB / 16; ++ks) {     // contraction over the 64 queries of the tile
+          umma_ts(tmem + C_DV, tmem + C_ST + ks * 8, make_desc_nosw(dop + ks * 256, 128, zp - dop), IDESC_BKV, (j > 0 || ks > 0) ? 1u : 0u);
+          umma_ts(tmem + C_DK, tmem + C_DPT + ks * 8, make_desc_nosw(qp + ks * 256, 128, zp - qp), IDESC_BKV, (j > 0 || ks > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int ks = 0; ks < 128 / 16; ++ks)       // contraction over the CTA's 128 keys
+          umma_ss(tmem + C_DQ + (j & 1) * 16, make_desc_nosw(dsb + ks * 256, 128, PANEL), make_desc_nosw(km + ks * 256, 128, zp - km),
+                  IDESC_BQ, ks > 0 ? 1u : 0u);
+        umma_commit(q_empty + 8 * st);
+        umma_commit(dq_full + 8 * (j & 1));
+      }
+      __syncwarp();
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;                               // key row = TMEM lane
+    const uint32_t trow = tmem + ((uint32_t)(quad * 32) << 16);
+    const float sl2 = scale * LOG2E;
+    float* dqb = dq_acc + (long long)b * N * C + head * D;
+    auto drain_dq = [&](int j) {                                    // dQ tile of sweep step j -> fp32 accumulator
+      mbar_wait(dq_full + 8 * (j & 1), (j >> 1) & 1);
+      tc_fence_after();
+      uint32_t r16[16];
+      tmem_ld16(trow + C_DQ + (j & 1) * 16, r16);
+      int jt = j + rot; if (jt >= ntiles) jt -= ntiles;
+      if (lane < 16) {                                              // M = 64: rows 16*quad + lane sit in lanes 0..15 of each quadrant
+        float* dst = dqb + (long long)(jt * TQB + quad * 16 + lane) * C;
+        if (D == 8) {
+          red_add_v4(dst, __uint_as_float(r16[0]), __uint_as_float(r16[1]), __uint_as_float(r16[2]), __uint_as_float(r16[3]));
+          red_add_v4(dst + 4, __uint_as_float(r16[4]), __uint_as_float(r16[5]), __uint_as_float(r16[6]), __uint_as_float(r16[7]));
+        } else {
+          // (selects, not r16[4 * head + i]: a run-time register index would put the array in local memory)
+          red_add_v4(dst, __uint_as_float(head ? r16[4] : r16[0]), __uint_as_float(head ? r16[5] : r16[1]),
+                     __uint_as_float(head ? r16[6] : r16[2]), __uint_as_float(head ? r16[7] : r16[3]));
+        }
+      }
+    };
+    for (int j = 0; j < ntiles; ++j) {
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      uint8_t* dsb = smem + B_OFF_DS + (j & 1) * DSBUF + row * 16;
+#pragma unroll
+      for (int c = 0; c < TQB / 32; ++c) {
+        uint32_t s32[32], d32[32], pk[16], dk16[16];
+        tmem_ld32(trow + C_ST + c * 32, s32);
+        tmem_ld32(trow + C_DPT + c * 32, d32);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float x0, x1, e0, e1;
+          mul2(x0, x1, __uint_as_float(s32[2 * i]), __uint_as_float(s32[2 * i + 1]), sl2, sl2);
+          if (POLY > 0 && (i % (POLY > 0 ? POLY : 1)) == (POLY > 0 ? POLY : 1) - 1) {
+            ex2_poly2(x0, x1, x0, x1);
+          } else {
+            x0 = ex2(x0);
+            x1 = ex2(x1);
+          }
+          mul2(e0, e1, x0, x1, __uint_as_float(d32[2 * i]), __uint_as_float(d32[2 * i + 1]));
+          pk[i] = pack_bf16(x0, x1);
+          dk16[i] = pack_bf16(e0, e1);
+        }
+        tmem_st16(trow + C_ST + c * 16, pk);                        // P^T over consumed S'^T columns
+        tmem_st16(trow + C_DPT + c * 16, dk16);                     // dS^T over consumed dP'^T columns
+#pragma unroll
+        for (int blk = 0; blk < 4; ++blk)                           // dS, M-major: query block (4c + blk), this key row
+          *reinterpret_cast<uint4*>(dsb + (c * 4 + blk) * PANEL) = make_uint4(dk16[4 * blk], dk16[4 * blk + 1], dk16[4 * blk + 2], dk16[4 * blk + 3]);
+      }
+      tmem_st_wait();
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+      if (j > 0) drain_dq(j - 1);
+    }
+    drain_dq(ntiles - 1);                                           // also: every dV / dK product has completed
+    uint32_t r16[16];
+    bf16* pk_ = dk + ((long long)b * N + k0 + row) * lddk + head * D;
+    bf16* pv_ = dv + ((long long)b * N + k0 + row) * lddv + head * D;
+    tmem_ld16(trow + C_DK, r16);
+    if (D == 8) {
+      *reinterpret_cast<uint4*>(pk_) = make_uint4(pack_bf16(__uint_as_float(r16[0]) * scale, __uint_as_float(r16[1]) * scale),
+                                                  pack_bf16(__uint_as_float(r16[2]) * scale, __uint_as_float(r16[3]) * scale),
+                                                  pack_bf16(__uint_as_float(r16[4]) * scale, __uint_as_float(r16[5]) * scale),
+                                                  pack_bf16(__uint_as_float(r16[6]) * scale, __uint_as_float(r16[7]) * scale));
+    } else {
+      *reinterpret_cast<uint2*>(pk_) = make_uint2(pack_bf16(__uint_as_float(head ? r16[4] : r16[0]) * scale, __uint_as_float(head ? r16[5] : r16[1]) * scale),
+                                                  pack_bf16(__uint_as_float(head ? r16[6] : r16[2]) * scale, __uint_as_float(head ? r16[7] : r16[3]) * scale));
+    }
+    tmem_ld16(trow + C_DV, r16);
+    if (D == 8) {
+      *reinterpret_cast<uint4*>(pv_) = make_uint4(pack_bf16(__uint_as_float(r16[0]), __uint_as_float(r16[1])),
+                                                  pack_bf16(__uint_as_float(r16[2]), __uint_as_float(r16[3])),
+                                                  pack_bf16(__uint_as_float(r16[4]), __uint_as_float(r16[5])),
+                                                  pack_bf16(__uint_as_float(r16[6]), __uint_as_float(r16[7])));
+    } else {
+      *reinterpret_cast<uint2*>(pv_) = make_uint2(pack_bf16(__uint_as_float(head ? r16[4] : r16[0]), __uint_as_float(head ? r16[5] : r16[1])),
+                                                  pack_bf16(__uint_as_float(head ? r16[6] : r16[2]), __uint_as_float(head ? r16[7] : r16[3])));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+__global__ void attn_dq_cast_tc_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long rows, int C, int lddq, float scale) {
+  const int cv = C / 2;
+  const long long total = rows * cv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cv;
+    const int c = (int)(i - r * cv) * 2;
+    const float2 a = *reinterpret_cast<const float2*>(acc + r * C + c);
+    *reinterpret_cast<uint32_t*>(dq + r * lddq + c) = pack_bf16(a.x * scale, a.y * scale);
   }
 }
 
@@ -343,10 +626,10 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 // [rows, C] bf16 with row pitch ld elements -> boxes of {8 channels, 128 rows}, no swizzle
-int make_map_rows(CUtensorMap* m, const void* ptr, long long rows, int C, int ld) {
+int make_map_rows(CUtensorMap* m, const void* ptr, long long rows, int C, int ld, int box_rows = TK) {
   cuuint64_t dims[2] = {(cuuint64_t)C, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {8, (cuuint32_t)TK};
+  cuuint32_t box[2] = {8, (cuuint32_t)box_rows};
   cuuint32_t es[2] = {1, 1};
   CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -393,5 +676,70 @@ extern "C" int hn_attn_fwd_tc(const void* q, const void* k, const void* v, void*
   }
 #undef LAUNCH_TC
   HN_CHECK_LAUNCH("attn_fwd_tc");
+  return HN_OK;
+}
+
+// workspace of the tcgen05 backward, fp32 elements: two auxiliary panels (bf16 [B, heads, N, 8] each) + the fp32 dQ accumulator
+extern "C" long long hn_attn_bwd_tc_workspace(int B, int N, int heads, int D) {
+  const long long rows = (long long)B * heads * N;
+  return rows * 8 + (long long)B * N * heads * D;
+}
+
+extern "C" int hn_attn_bwd_tc_supported(int N, int D, int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk, int lddv) {
+  if (D != 4 && D != 8) return 0;
+  if (N <= 0 || N % 128) return 0;
+  if (ldq % 8 || ldk % 8 || ldv % 8 || lddo % 8 || ldo % 2 || lddq % 2 || lddk % 4 || lddv % 4) return 0;
+  return get_encode() != nullptr ? 1 : 0;
+}
+
+extern "C" int hn_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
+                              float* ws, long long ws_floats, void* dq, void* dk, void* dv, int B, int N, int heads, int D,
+                              int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk, int lddv, float scale,
+                              int poly_every, void* stream) {
+  HN_REQUIRE(q && k && v && o && dout && lse && ws && dq && dk && dv && B > 0 && heads == 2, "attn_bwd_tc: bad args");
+  HN_REQUIRE(hn_attn_bwd_tc_supported(N, D, ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv), "attn_bwd_tc: shape not supported");
+  HN_REQUIRE(ws_floats >= hn_attn_bwd_tc_workspace(B, N, heads, D), "attn_bwd_tc: workspace too small (hn_attn_bwd_tc_workspace)");
+  HN_REQUIRE(((uintptr_t)q | (uintptr_t)k | (uintptr_t)v | (uintptr_t)dout | (uintptr_t)dk | (uintptr_t)dv | (uintptr_t)ws) % 16 == 0, "attn_bwd_tc: 16B alignment");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = heads * D;
+  const long long rows = (long long)B * heads * N;
+  uint4* auxL = reinterpret_cast<uint4*>(ws);
+  uint4* auxD = auxL + rows;
+  float* dq_acc = ws + rows * 8;
+  attn_bwd_prep_kernel<<<hn_cdiv(rows, 256), 256, 0, st>>>((const bf16*)o, (const bf16*)dout, lse, auxL, auxD, N, heads, D, ldo, lddo,
+                                                         1.f / scale, rows);
+  HN_CHECK_LAUNCH("attn_bwd_prep");
+  cudaError_t e = cudaMemsetAsync(dq_acc, 0, sizeof(float) * (size_t)B * N * C, st);
+  if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "attn_bwd_tc: memset: %s", cudaGetErrorString(e));
+  CUtensorMap mq, mdo, ml, md;
+  int rc = make_map_rows(&mq, q, (long long)B * N, C, ldq, TQB);
+  if (!rc) rc = make_map_rows(&mdo, dout, (long long)B * N, C, lddo, TQB);
+  if (!rc) rc = make_map_rows(&ml, auxL, rows, 8, 8, TQB);
+  if (!rc) rc = make_map_rows(&md, auxD, rows, 8, 8, TQB);
+  if (rc) HN_FAIL(HN_ECUDA, "attn_bwd_tc: cuTensorMapEncodeTiled = %d", rc);
+  dim3 grid(N / 128, heads, B);
+#define LAUNCH_BTC(DD, PL)                                                                                              \
+  do {                                                                                                                   \
+    static bool configured = false;                                                                                      \
+    if (!configured) {                                                                                                   \
+      cudaError_t e2 = cudaFuncSetAttribute(attn_bwd_tc_kernel<DD, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM); \
+      if (e2 != cudaSuccess) HN_FAIL(HN_ECUDA, "attn_bwd_tc: smem attribute: %s", cudaGetErrorString(e2));               \
+      configured = true;                                                                                                 \
+    }                                                                                                                    \
+    attn_bwd_tc_kernel<DD, PL><<<grid, TC_THREADS, B_SMEM, st>>>(mq, mdo, ml, md, (const bf16*)k, (const bf16*)v, dq_acc, (bf16*)dk, \
+                                                               (bf16*)dv, N, heads, ldk, ldv, lddk, lddv, C, scale);    \
+  } while (0)
+  if (D == 4) {
+    if (poly_every == 4) LAUNCH_BTC(4, 4); else if (poly_every == 3) LAUNCH_BTC(4, 3); else if (poly_every == 2) LAUNCH_BTC(4, 2); else LAUNCH_BTC(4, 0);
+  } else {
+    if (poly_every == 4) LAUNCH_BTC(8, 4); else if (poly_every == 3) LAUNCH_BTC(8, 3); else if (poly_every == 2) LAUNCH_BTC(8, 2); else LAUNCH_BTC(8, 0);
+  }
+#undef LAUNCH_BTC
+  HN_CHECK_LAUNCH("attn_bwd_tc");
+  const long long prow = (long long)B * N;
+  long long blocks = (prow * (C / 2) + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  attn_dq_cast_tc_kernel<<<(int)blocks, 256, 0, st>>>(dq_acc, (bf16*)dq, prow, C, lddq, scale);
+  HN_CHECK_LAUNCH("attn_dq_cast_tc");
   return HN_OK;
 }

@@ -358,6 +358,13 @@ def invalidate_packed():
         ent["ver"] = (None, ent["ver"][1])
 
 
+def clear_packed():
+    """Drop every derived bf16 weight copy and its buffers.  NOT safe while a captured CUDA graph or the
+    hn_pack_weight_multi job table still refers to them: for tests and for tearing a model down."""
+    _pack_cache.clear()
+    _repack_table.update(sig=None, dev=None, n=0, max=1)
+
+
 def _desc(**kw):
     d = HnConv()
     for k, v in kw.items():
@@ -1171,6 +1178,8 @@ def dwconv_relu_ln_qkv(x, w, b, gamma, beta, eps=1e-5):
 
 ATTN_FWD_TC = False          # tcgen05 / TMEM / TMA attention forward for D in {4, 8}, N % 128 == 0 (hn_attn_fwd_tc)
 ATTN_FWD_TC_POLY = 0         # share of its exponentials on the FMA pipe: every n-th pair (0 = none)
+ATTN_BWD_TC = False          # tcgen05 / TMEM / TMA one-pass attention backward for the same shapes (hn_attn_bwd_tc)
+ATTN_BWD_TC_POLY = 0
 
 
 class _AttnFn(torch.autograd.Function):
@@ -1207,6 +1216,14 @@ class _AttnFn(torch.autograd.Function):
         heads = ctx.heads
         N, D = H * W, C // heads
         dqkv = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=q.device)
+        lib = _lib.load()
+        if ATTN_BWD_TC and heads == 2 and lib.hn_attn_bwd_tc_supported(N, D, ldq, ldk, ldv, C, lddo, C, C, C):
+            nws = lib.hn_attn_bwd_tc_workspace(B, N, heads, D)
+            ws = torch.empty(nws, dtype=torch.float32, device=q.device)
+            call("hn_attn_bwd_tc", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(),
+                 ws.data_ptr(), nws, dqkv[0].data_ptr(), dqkv[1].data_ptr(), dqkv[2].data_ptr(), B, N, heads, D, ldq, ldk,
+                 ldv, C, lddo, C, C, C, ctx.scale, ATTN_BWD_TC_POLY, _stream())
+            return dqkv[0], dqkv[1], dqkv[2], None
         nws = _lib.load().hn_attn_bwd_workspace(B, N, heads, D)
         ws = torch.empty(nws, dtype=torch.float32, device=q.device)
         call("hn_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(),
