@@ -31,7 +31,8 @@ constexpr int PANEL = TK * 16;   // one {8 ch, 128 rows} box
 constexpr int NST = 4;           // K/V stages
 constexpr int TC_THREADS = 192;
 constexpr int TMEM_COLS = 256;
-constexpr int COL_O = 128;
+constexpr int COL_P = 128;         // P (bf16 pairs, 64 columns) has its own columns: S of the next tile is issued before P V
+constexpr int COL_O = 192;
 
 // ---- PTX wrappers (as in hn_conv_tc.cu) -------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -130,6 +131,39 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// loads without the wait: the caller overlaps them with arithmetic on the previous chunk and waits once (tmem_ld_wait
+// covers every tcgen05.ld issued so far by the thread)
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// the same wait, carrying the destination registers as read-write operands: arithmetic on them (non-volatile inline asm,
+// plain FP ops) can then not be scheduled above the wait by the compiler
+__device__ __forceinline__ void tmem_ld_wait32(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31]) :: "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait16(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]) :: "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
 
 // Shared-memory matrix descriptor, no swizzle (INTERLEAVE): core matrix = 8 rows x 16 bytes, contiguous.
 //   K-major operand  (rows = M/N index, 16 B = 8 K elements): SBO = bytes between 8-row groups, LBO = bytes between the
@@ -220,26 +254,40 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
   } else if (warp == 1) {
     const bool leader = elect_one();
     const uint64_t adesc = make_desc_nosw(sbase + OFF_Q, OFF_ZERO - OFF_Q, 128);
+    // S(0); then per tile: [P(j) ready] -> S(j+1) FIRST (the softmax warps start the next tile as soon as it lands),
+    // then O += P(j) [V | 1] (off the critical path)
+    mbar_wait(kv_full, 0);
+    tc_fence_after();
+    if (leader) {
+      const uint32_t kp0 = sbase + OFF_KV;
+      umma_ss(tmem, adesc, make_desc_nosw(kp0, sbase + OFF_ZERO - kp0, 128), IDESC_S, 0u);
+      umma_commit(s_full);
+    }
+    __syncwarp();
     for (int j = 0; j < ntiles; ++j) {
       const int st = j % NST;
-      const uint32_t kp = sbase + OFF_KV + st * 2 * PANEL, vp = kp + PANEL;
-      mbar_wait(kv_full + 8 * st, (j / NST) & 1);
-      tc_fence_after();
-      if (leader) {
-        umma_ss(tmem, adesc, make_desc_nosw(kp, sbase + OFF_ZERO - kp, 128), IDESC_S, 0u);
-        umma_commit(s_full);
-      }
-      __syncwarp();
+      const uint32_t vp = sbase + OFF_KV + st * 2 * PANEL + PANEL;
       mbar_wait(p_full, j & 1);
       tc_fence_after();
+      if (j + 1 < ntiles) {
+        const int sn = (j + 1) % NST;
+        mbar_wait(kv_full + 8 * sn, ((j + 1) / NST) & 1);
+        tc_fence_after();
+        if (leader) {
+          const uint32_t kp = sbase + OFF_KV + sn * 2 * PANEL;
+          umma_ss(tmem, adesc, make_desc_nosw(kp, sbase + OFF_ZERO - kp, 128), IDESC_S, 0u);
+          umma_commit(s_full);
+        }
+        __syncwarp();
+      }
       if (leader) {
 #pragma unroll
         for (int ks = 0; ks < TK / 16; ++ks) {
           // B = [V | 1] MN-major: 16 key rows of this K step (two 8-row groups 128 B apart), N blocks: V panel, ones panel
           const uint64_t bdesc = make_desc_nosw(vp + ks * 256, 128, sbase + OFF_ONES - vp);
-          umma_ts(tmem + COL_O, tmem + ks * 8, bdesc, IDESC_PV, (j > 0 || ks > 0) ? 1u : 0u);
+          umma_ts(tmem + COL_O, tmem + COL_P + ks * 8, bdesc, IDESC_PV, (j > 0 || ks > 0) ? 1u : 0u);
         }
-        umma_commit(kv_empty + 8 * st);
+        umma_commit(kv_empty + 8 * st);          // = "P V (j) done": K/V stage free, P columns free, O stable
         if (j == ntiles - 1) umma_commit(o_full);
       }
       __syncwarp();
@@ -254,13 +302,24 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
     for (int j = 0; j < ntiles; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      uint32_t r[32];
+      uint32_t ra[32], rb[32];
       float m_tile = -INFINITY;
+      // pass 1: row maximum; the load of chunk c + 1 is in flight while chunk c is reduced
+      tmem_ld32_nowait(trow, ra);
 #pragma unroll
       for (int c = 0; c < TK / 32; ++c) {
-        tmem_ld32(trow + c * 32, r);
+        uint32_t* cur = (c & 1) ? rb : ra;
+        uint32_t* nxt = (c & 1) ? ra : rb;
+        tmem_ld_wait32(cur);
+        if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
+        else tmem_ld32_nowait(trow, nxt);                          // chunk 0 again, for pass 2
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+        for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+      }
+      // the previous tile's P V must be done before its P columns are overwritten / O is rescaled
+      if (j > 0) {
+        mbar_wait(kv_empty + 8 * ((j - 1) % NST), ((j - 1) / NST) & 1);
+        tc_fence_after();
       }
       // lazy rescale: move the reference only when this tile exceeds it by more than 2^8 (probabilities stay < 256)
       const bool need = (m_tile - m_ref) * sl2 > 8.f;
@@ -276,14 +335,18 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
         if (need) m_ref = m_tile;
       }
       const float moff = -m_ref * sl2;
+      // pass 2 (chunk 0 was requested into ra/rb above: TK / 32 is even, so it sits in ra)
 #pragma unroll
       for (int c = 0; c < TK / 32; ++c) {
-        tmem_ld32(trow + c * 32, r);
+        uint32_t* cur = (c & 1) ? rb : ra;
+        uint32_t* nxt = (c & 1) ? ra : rb;
+        tmem_ld_wait32(cur);
+        if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float x0, x1;
-          fma2(x0, x1, __uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]), sl2, moff);
+          fma2(x0, x1, __uint_as_float(cur[2 * i]), __uint_as_float(cur[2 * i + 1]), sl2, moff);
           if (POLY > 0 && (i % (POLY > 0 ? POLY : 1)) == (POLY > 0 ? POLY : 1) - 1) {
             ex2_poly2(x0, x1, x0, x1);
           } else {
@@ -292,7 +355,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
           }
           pk[i] = pack_bf16(x0, x1);
         }
-        tmem_st16(trow + c * 16, pk);          // P over the S columns already consumed
+        tmem_st16(trow + COL_P + c * 16, pk);
       }
       tmem_st_wait();
       tc_fence_before();
@@ -358,7 +421,7 @@ constexpr int B_OFF_DS = B_OFF_ST + NSTB * 4 * QPANEL;
 constexpr int B_OFF_E = B_OFF_DS + 2 * DSBUF;
 constexpr int B_OFF_Z = B_OFF_E + PANEL;
 constexpr int B_SMEM = B_OFF_Z + PANEL;
-constexpr int C_ST = 0, C_DPT = 64, C_DV = 128, C_DK = 144, C_DQ = 160;     // TMEM columns
+constexpr int C_ST = 0, C_DPT = 64, C_PT = 128, C_DST = 160, C_DV = 192, C_DK = 208, C_DQ = 224;     // TMEM columns (256)
 constexpr uint32_t IDESC_BS = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TQB >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 constexpr uint32_t IDESC_BKV = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(16 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 constexpr uint32_t IDESC_BQ = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(16 >> 3) << 17) | ((uint32_t)(TQB >> 4) << 24);
@@ -408,7 +471,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
                    const bf16* __restrict__ k, const bf16* __restrict__ v, float* __restrict__ dq_acc, bf16* __restrict__ dk,
                    bf16* __restrict__ dv, int N, int heads, int ldk, int ldv, int lddk, int lddv, int C, float scale) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bars[2 * NSTB + 4];
+  __shared__ __align__(8) uint64_t bars[2 * NSTB + 5];
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.y, b = blockIdx.z;
@@ -420,6 +483,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
   const uint32_t q_full = smem_u32(&bars[0]), q_empty = smem_u32(&bars[NSTB]);
   const uint32_t s_full = smem_u32(&bars[2 * NSTB]), p_full = smem_u32(&bars[2 * NSTB + 1]);
   const uint32_t dq_full = smem_u32(&bars[2 * NSTB + 2]);          // two barriers: dQ buffer 0 / 1
+  const uint32_t pt_free = smem_u32(&bars[2 * NSTB + 4]);
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NSTB; ++s) { mbar_init(q_full + 8 * s, 1); mbar_init(q_empty + 8 * s, 1); }
@@ -427,6 +491,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
     mbar_init(p_full, 4);
     mbar_init(dq_full, 1);
     mbar_init(dq_full + 8, 1);
+    mbar_init(pt_free, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -479,26 +544,41 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
     const bool leader = elect_one();
     const uint32_t km = sbase + B_OFF_KM, vm = sbase + B_OFF_VM, ep = sbase + B_OFF_E, zp = sbase + B_OFF_Z;
     const uint64_t a_k = make_desc_nosw(km, ep - km, 128), a_v = make_desc_nosw(vm, ep - vm, 128);
+    // S'(0), dP'(0); then per tile: [P^T(j), dS^T(j) ready] -> S'(j+1), dP'(j+1) FIRST, then the accumulating products of tile j
+    mbar_wait(q_full, 0);
+    tc_fence_after();
+    if (leader) {
+      const uint32_t qp0 = sbase + B_OFF_ST;
+      umma_ss(tmem + C_ST, a_k, make_desc_nosw(qp0, QPANEL, 128), IDESC_BS, 0u);
+      umma_ss(tmem + C_DPT, a_v, make_desc_nosw(qp0 + 2 * QPANEL, QPANEL, 128), IDESC_BS, 0u);
+      umma_commit(s_full);
+    }
+    __syncwarp();
     for (int j = 0; j < ntiles; ++j) {
       const int st = j % NSTB;
       const uint32_t qp = sbase + B_OFF_ST + st * 4 * QPANEL, dop = qp + 2 * QPANEL;
       const uint32_t dsb = sbase + B_OFF_DS + (j & 1) * DSBUF;
-      mbar_wait(q_full + 8 * st, (j / NSTB) & 1);
-      tc_fence_after();
-      if (leader) {
-        umma_ss(tmem + C_ST, a_k, make_desc_nosw(qp, QPANEL, 128), IDESC_BS, 0u);
-        umma_ss(tmem + C_DPT, a_v, make_desc_nosw(dop, QPANEL, 128), IDESC_BS, 0u);
-        umma_commit(s_full);
-      }
-      __syncwarp();
       mbar_wait(p_full, j & 1);
       tc_fence_after();
+      if (j + 1 < ntiles) {
+        const int sn = (j + 1) % NSTB;
+        mbar_wait(q_full + 8 * sn, ((j + 1) / NSTB) & 1);
+        tc_fence_after();
+        if (leader) {
+          const uint32_t qn = sbase + B_OFF_ST + sn * 4 * QPANEL;
+          umma_ss(tmem + C_ST, a_k, make_desc_nosw(qn, QPANEL, 128), IDESC_BS, 0u);
+          umma_ss(tmem + C_DPT, a_v, make_desc_nosw(qn + 2 * QPANEL, QPANEL, 128), IDESC_BS, 0u);
+          umma_commit(s_full);
+        }
+        __syncwarp();
+      }
       if (leader) {
 #pragma unroll
         for (int ks = 0; ks < TQB / 16; ++ks) {     // contraction over the 64 queries of the tile
-          umma_ts(tmem + C_DV, tmem + C_ST + ks * 8, make_desc_nosw(dop + ks * 256, 128, zp - dop), IDESC_BKV, (j > 0 || ks > 0) ? 1u : 0u);
-          umma_ts(tmem + C_DK, tmem + C_DPT + ks * 8, make_desc_nosw(qp + ks * 256, 128, zp - qp), IDESC_BKV, (j > 0 || ks > 0) ? 1u : 0u);
+          umma_ts(tmem + C_DV, tmem + C_PT + ks * 8, make_desc_nosw(dop + ks * 256, 128, zp - dop), IDESC_BKV, (j > 0 || ks > 0) ? 1u : 0u);
+          umma_ts(tmem + C_DK, tmem + C_DST + ks * 8, make_desc_nosw(qp + ks * 256, 128, zp - qp), IDESC_BKV, (j > 0 || ks > 0) ? 1u : 0u);
         }
+        umma_commit(pt_free);                       // P^T / dS^T columns may be overwritten by the next tile
 #pragma unroll
         for (int ks = 0; ks < 128 / 16; ++ks)       // contraction over the CTA's 128 keys
           umma_ss(tmem + C_DQ + (j & 1) * 16, make_desc_nosw(dsb + ks * 256, 128, PANEL), make_desc_nosw(km + ks * 256, 128, zp - km),
@@ -536,30 +616,43 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
       mbar_wait(s_full, j & 1);
       tc_fence_after();
       uint8_t* dsb = smem + B_OFF_DS + (j & 1) * DSBUF + row * 16;
+      uint32_t sa[16], sb[16], da[16], db[16];
+      tmem_ld16_nowait(trow + C_ST, sa);
+      tmem_ld16_nowait(trow + C_DPT, da);
 #pragma unroll
-      for (int c = 0; c < TQB / 32; ++c) {
-        uint32_t s32[32], d32[32], pk[16], dk16[16];
-        tmem_ld32(trow + C_ST + c * 32, s32);
-        tmem_ld32(trow + C_DPT + c * 32, d32);
+      for (int c = 0; c < TQB / 16; ++c) {
+        uint32_t* s16 = (c & 1) ? sb : sa;
+        uint32_t* d16 = (c & 1) ? db : da;
+        tmem_ld_wait16(s16);
+        tmem_ld_wait16(d16);
+        if (c + 1 < TQB / 16) {                                    // next 16 columns in flight during the arithmetic
+          tmem_ld16_nowait(trow + C_ST + (c + 1) * 16, (c & 1) ? sa : sb);
+          tmem_ld16_nowait(trow + C_DPT + (c + 1) * 16, (c & 1) ? da : db);
+        }
+        uint32_t pk[8], dk8[8];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
+        for (int i = 0; i < 8; ++i) {
           float x0, x1, e0, e1;
-          mul2(x0, x1, __uint_as_float(s32[2 * i]), __uint_as_float(s32[2 * i + 1]), sl2, sl2);
+          mul2(x0, x1, __uint_as_float(s16[2 * i]), __uint_as_float(s16[2 * i + 1]), sl2, sl2);
           if (POLY > 0 && (i % (POLY > 0 ? POLY : 1)) == (POLY > 0 ? POLY : 1) - 1) {
             ex2_poly2(x0, x1, x0, x1);
           } else {
             x0 = ex2(x0);
             x1 = ex2(x1);
           }
-          mul2(e0, e1, x0, x1, __uint_as_float(d32[2 * i]), __uint_as_float(d32[2 * i + 1]));
+          mul2(e0, e1, x0, x1, __uint_as_float(d16[2 * i]), __uint_as_float(d16[2 * i + 1]));
           pk[i] = pack_bf16(x0, x1);
-          dk16[i] = pack_bf16(e0, e1);
+          dk8[i] = pack_bf16(e0, e1);
         }
-        tmem_st16(trow + C_ST + c * 16, pk);                        // P^T over consumed S'^T columns
-        tmem_st16(trow + C_DPT + c * 16, dk16);                     // dS^T over consumed dP'^T columns
-#pragma unroll
-        for (int blk = 0; blk < 4; ++blk)                           // dS, M-major: query block (4c + blk), this key row
-          *reinterpret_cast<uint4*>(dsb + (c * 4 + blk) * PANEL) = make_uint4(dk16[4 * blk], dk16[4 * blk + 1], dk16[4 * blk + 2], dk16[4 * blk + 3]);
+        if (c == 0 && j > 0) {                                      // the previous tile's dV / dK products have read P^T / dS^T
+          mbar_wait(pt_free, (j - 1) & 1);
+          tc_fence_after();
+        }
+        tmem_st8(trow + C_PT + c * 8, pk);
+        tmem_st8(trow + C_DST + c * 8, dk8);
+        // dS, M-major: query blocks 2c and 2c + 1, this key row
+        *reinterpret_cast<uint4*>(dsb + (2 * c) * PANEL) = make_uint4(dk8[0], dk8[1], dk8[2], dk8[3]);
+        *reinterpret_cast<uint4*>(dsb + (2 * c + 1) * PANEL) = make_uint4(dk8[4], dk8[5], dk8[6], dk8[7]);
       }
       tmem_st_wait();
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
