@@ -20,7 +20,15 @@ nws = _lib.load().hn_attn_bwd_workspace(B, N, heads, D)
 ws = torch.empty(nws, dtype=torch.float32, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 scale = 1.0 / math.sqrt(D)
+TC = len(sys.argv) > 2 and sys.argv[2] == "tc"
+nws_tc = _lib.load().hn_attn_bwd_tc_workspace(B, N, heads, D)
+ws_tc = torch.empty(nws_tc, dtype=torch.float32, device=dev)
 for _ in range(2):
+    if TC:
+        call("hn_attn_fwd_tc", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D, C, C, C, C, scale, 3, st)
+        call("hn_attn_bwd_tc", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(), ws_tc.data_ptr(), nws_tc,
+             dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, N, heads, D, C, C, C, C, C, C, C, C, scale, 3, st)
+        continue
     call("hn_attn_fwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), lse.data_ptr(), B, N, heads, D, C, C, C, C, scale, st)
     call("hn_attn_bwd", q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(), ws.data_ptr(), nws,
          dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, N, heads, D, C, C, C, C, C, C, C, C, scale, st)

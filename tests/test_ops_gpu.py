@@ -374,14 +374,14 @@ def test_flash_attention(ops, D, N, tc):
     """softmax(QK^T/sqrt(d))V, heads=2, incl. ragged N (not a multiple of the 64-token tile).
     tc > 0: the tcgen05 / TMEM / TMA forward (hn_attn_fwd_tc); tc = 2, 3: with every 2nd / 3rd exponential pair on the
     FMA-pipe polynomial."""
-    if tc:                        # tc >= 10: the tcgen05 backward (hn_attn_bwd_tc) as well
-        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = True, (0 if tc % 10 == 1 else tc % 10)
-        ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY = tc >= 10, (0 if tc % 10 == 1 else tc % 10)
+    saved = (ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY, ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY)
+    # tc == 0: the mma.sync kernels; tc >= 10: the tcgen05 backward (hn_attn_bwd_tc) as well
+    ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = tc > 0, (0 if tc % 10 <= 1 else tc % 10)
+    ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY = tc >= 10, (0 if tc % 10 <= 1 else tc % 10)
     try:
         _flash_attention_case(ops, D, N)
     finally:
-        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY = False, 0
-        ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY = False, 0
+        ops.ATTN_FWD_TC, ops.ATTN_FWD_TC_POLY, ops.ATTN_BWD_TC, ops.ATTN_BWD_TC_POLY = saved
 
 
 def _flash_attention_case(ops, D, N):

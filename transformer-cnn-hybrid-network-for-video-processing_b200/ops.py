@@ -1176,10 +1176,13 @@ def dwconv_relu_ln_qkv(x, w, b, gamma, beta, eps=1e-5):
     return _DwLnQKVFn.apply(x, w, b, gamma, beta, eps)
 
 
-ATTN_FWD_TC = False          # tcgen05 / TMEM / TMA attention forward for D in {4, 8}, N % 128 == 0 (hn_attn_fwd_tc)
-ATTN_FWD_TC_POLY = 0         # share of its exponentials on the FMA pipe: every n-th pair (0 = none)
-ATTN_BWD_TC = False          # tcgen05 / TMEM / TMA one-pass attention backward for the same shapes (hn_attn_bwd_tc)
-ATTN_BWD_TC_POLY = 0
+# tcgen05 / TMEM / TMA attention for the exponential-bound shapes (D in {4, 8}, two heads, N % 128 == 0: FCT blocks
+# 1, 2, 8, 9 = 99 % of the score elements); every other shape takes the mma.sync kernels.  POLY: every n-th pair of
+# exponentials on the FMA pipe (measured on B200, scripts/attn_bench.py: n = 3 is the fastest for both directions).
+ATTN_FWD_TC = True
+ATTN_FWD_TC_POLY = 3
+ATTN_BWD_TC = True
+ATTN_BWD_TC_POLY = 3
 
 
 class _AttnFn(torch.autograd.Function):
