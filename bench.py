@@ -159,6 +159,8 @@ WORK = {
     "hn_conv_wgrad_sc": lambda a: _conv_work(a),
     "hn_attn_fwd": lambda a: _attn_work(a, False),
     "hn_attn_bwd": lambda a: _attn_work(a, True),
+    "hn_attn_fwd_tc": lambda a: _attn_work(a, False),          # same argument positions for B, N, heads, D
+    "hn_attn_bwd_tc": lambda a: _attn_work(a, True),
 }
 
 
