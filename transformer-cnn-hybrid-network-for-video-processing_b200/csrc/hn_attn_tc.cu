@@ -29,7 +29,7 @@ constexpr int TQ = 128;          // queries per CTA = TMEM lanes
 constexpr int TK = 128;          // keys per tile
 constexpr int PANEL = TK * 16;   // one {8 ch, 128 rows} box
 constexpr int NST = 4;           // K/V stages
-constexpr int TC_THREADS = 320;   // TMA warp, MMA warp, 8 softmax warps: two per TMEM lane quadrant, each takes half of the columns
+constexpr int TC_THREADS = 192;
 constexpr int TMEM_COLS = 256;
 constexpr int COL_P = 128;         // P (bf16 pairs, 64 columns) has its own columns: S of the next tile is issued before P V
 constexpr int COL_O = 192;
@@ -131,8 +131,6 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-// named barrier of the two softmax warps that share a lane quadrant
-__device__ __forceinline__ void pair_sync(int quad) { asm volatile("bar.sync %0, 64;" ::"r"(quad + 1) : "memory"); }
 // loads without the wait: the caller overlaps them with arithmetic on the previous chunk and waits once (tmem_ld_wait
 // covers every tcgen05.ld issued so far by the thread)
 __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t* r) {
@@ -200,7 +198,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[2 * NST + 3];
   __shared__ uint32_t tmem_slot;
-  __shared__ float s_mx[2][TQ];              // per-row maximum of each column half (exchanged between the warp pair)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.y, b = blockIdx.z;
   const int q0 = blockIdx.x * TQ;
@@ -212,7 +209,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) { mbar_init(kv_full + 8 * s, 1); mbar_init(kv_empty + 8 * s, 1); }
     mbar_init(s_full, 1);
-    mbar_init(p_full, 8);
+    mbar_init(p_full, 4);
     mbar_init(o_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -220,7 +217,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "n"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (warp >= 2 && warp < 6) {
+  if (warp >= 2) {
     // stage this CTA's 128 query rows (one per thread), the ones panel and the zero panel
     const int row = threadIdx.x - 64;
     uint4 qv;
@@ -297,39 +294,37 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
     }
   } else {
     // ---- softmax: thread = query row = TMEM lane ------------------------------------------------------------------------
-    const int quad = warp & 3, half = (warp - 2) >> 2;
+    const int quad = warp & 3;
     const int row = quad * 32 + lane;
     const uint32_t trow = tmem + ((uint32_t)(quad * 32) << 16);
-    const uint32_t scol = half * (TK / 2);                       // this warp's 64 score columns
     const float sl2 = scale * LOG2E;
     float m_ref = -INFINITY;                 // reference maximum of the exponent (raw score units)
     for (int j = 0; j < ntiles; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
       uint32_t ra[32], rb[32];
-      float m_half = -INFINITY;
-      // pass 1: row maximum over this warp's columns; the second chunk is in flight while the first is reduced
-      tmem_ld32_nowait(trow + scol, ra);
-      tmem_ld32_nowait(trow + scol + 32, rb);
-      tmem_ld_wait32(ra);
+      float m_tile = -INFINITY;
+      // pass 1: row maximum; the load of chunk c + 1 is in flight while chunk c is reduced
+      tmem_ld32_nowait(trow, ra);
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) m_half = max3(m_half, __uint_as_float(ra[i]), __uint_as_float(ra[i + 1]));
-      tmem_ld_wait32(rb);
+      for (int c = 0; c < TK / 32; ++c) {
+        uint32_t* cur = (c & 1) ? rb : ra;
+        uint32_t* nxt = (c & 1) ? ra : rb;
+        tmem_ld_wait32(cur);
+        if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
+        else tmem_ld32_nowait(trow, nxt);                          // chunk 0 again, for pass 2
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) m_half = max3(m_half, __uint_as_float(rb[i]), __uint_as_float(rb[i + 1]));
-      s_mx[half][row] = m_half;
-      pair_sync(quad);
-      const float m_tile = fmaxf(s_mx[0][row], s_mx[1][row]);
+        for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+      }
       // the previous tile's P V must be done before its P columns are overwritten / O is rescaled
       if (j > 0) {
         mbar_wait(kv_empty + 8 * ((j - 1) % NST), ((j - 1) / NST) & 1);
         tc_fence_after();
       }
-      // lazy rescale: move the reference only when this tile exceeds it by more than 2^8 (probabilities stay < 256);
-      // both warps of the pair take the same decision, the first one rescales O
+      // lazy rescale: move the reference only when this tile exceeds it by more than 2^8 (probabilities stay < 256)
       const bool need = (m_tile - m_ref) * sl2 > 8.f;
       if (__any_sync(0xffffffffu, need)) {
-        if (j > 0 && half == 0) {
+        if (j > 0) {
           const float alpha = need ? ex2((m_ref - m_tile) * sl2) : 1.f;
           uint32_t ov[16];
           tmem_ld16(trow + COL_O, ov);
@@ -340,10 +335,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
         if (need) m_ref = m_tile;
       }
       const float moff = -m_ref * sl2;
-      // pass 2: both chunks are still in registers
+      // pass 2 (chunk 0 was requested into ra/rb above: TK / 32 is even, so it sits in ra)
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t* cur = c ? rb : ra;
+      for (int c = 0; c < TK / 32; ++c) {
+        uint32_t* cur = (c & 1) ? rb : ra;
+        uint32_t* nxt = (c & 1) ? ra : rb;
+        tmem_ld_wait32(cur);
+        if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -357,7 +355,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
           }
           pk[i] = pack_bf16(x0, x1);
         }
-        tmem_st16(trow + COL_P + half * 32 + c * 16, pk);
+        tmem_st16(trow + COL_P + c * 16, pk);
       }
       tmem_st_wait();
       tc_fence_before();
@@ -366,7 +364,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
     }
     mbar_wait(o_full, 0);
     tc_fence_after();
-    if (half == 0) {
     uint32_t ov[16];
     tmem_ld16(trow + COL_O, ov);
     const float l = __uint_as_float(ov[8]);
@@ -386,7 +383,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
       *reinterpret_cast<uint2*>(op) = w;
     }
     lse[((long long)b * heads + head) * N + q0 + row] = m_ref * scale + logf(l);
-    }
   }
   tc_fence_before();
   __syncthreads();
@@ -492,7 +488,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
   if (threadIdx.x == 0) {
     for (int s = 0; s < NSTB; ++s) { mbar_init(q_full + 8 * s, 1); mbar_init(q_empty + 8 * s, 1); }
     mbar_init(s_full, 1);
-    mbar_init(p_full, 8);
+    mbar_init(p_full, 4);
     mbar_init(dq_full, 1);
     mbar_init(dq_full + 8, 1);
     mbar_init(pt_free, 1);
@@ -502,7 +498,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "n"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (warp >= 2 && warp < 6) {
+  if (warp >= 2) {
     const int row = threadIdx.x - 64;
     uint4 kv, vv;
     if (D == 8) {
@@ -593,7 +589,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
       __syncwarp();
     }
   } else {
-    const int quad = warp & 3, half = (warp - 2) >> 2;               // half: which 32 of the tile's 64 query columns
+    const int quad = warp & 3;
     const int row = quad * 32 + lane;                               // key row = TMEM lane
     const uint32_t trow = tmem + ((uint32_t)(quad * 32) << 16);
     const float sl2 = scale * LOG2E;
@@ -621,18 +617,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
       tc_fence_after();
       uint8_t* dsb = smem + B_OFF_DS + (j & 1) * DSBUF + row * 16;
       uint32_t sa[16], sb[16], da[16], db[16];
-      const int c0 = 2 * half;                                      // this warp's two 16-column chunks
-      tmem_ld16_nowait(trow + C_ST + c0 * 16, sa);
-      tmem_ld16_nowait(trow + C_DPT + c0 * 16, da);
-      tmem_ld16_nowait(trow + C_ST + (c0 + 1) * 16, sb);
-      tmem_ld16_nowait(trow + C_DPT + (c0 + 1) * 16, db);
+      tmem_ld16_nowait(trow + C_ST, sa);
+      tmem_ld16_nowait(trow + C_DPT, da);
 #pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
-        const int c = c0 + cc;
-        uint32_t* s16 = cc ? sb : sa;
-        uint32_t* d16 = cc ? db : da;
+      for (int c = 0; c < TQB / 16; ++c) {
+        uint32_t* s16 = (c & 1) ? sb : sa;
+        uint32_t* d16 = (c & 1) ? db : da;
         tmem_ld_wait16(s16);
         tmem_ld_wait16(d16);
+        if (c + 1 < TQB / 16) {                                    // next 16 columns in flight during the arithmetic
+          tmem_ld16_nowait(trow + C_ST + (c + 1) * 16, (c & 1) ? sa : sb);
+          tmem_ld16_nowait(trow + C_DPT + (c + 1) * 16, (c & 1) ? da : db);
+        }
         uint32_t pk[8], dk8[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -648,7 +644,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
           pk[i] = pack_bf16(x0, x1);
           dk8[i] = pack_bf16(e0, e1);
         }
-        if (cc == 0 && j > 0) {                                     // the previous tile's dV / dK products have read P^T / dS^T
+        if (c == 0 && j > 0) {                                      // the previous tile's dV / dK products have read P^T / dS^T
           mbar_wait(pt_free, (j - 1) & 1);
           tc_fence_after();
         }
@@ -663,39 +659,31 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap mapQ, const __grid_consta
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
-      if (j > 0 && ((j - 1) & 1) == half) drain_dq(j - 1);          // the two warps of a quadrant alternate
+      if (j > 0) drain_dq(j - 1);
     }
-    if (((ntiles - 1) & 1) == half) {
-      drain_dq(ntiles - 1);
-    } else {                                                        // every product of the sweep has completed
-      mbar_wait(dq_full + 8 * ((ntiles - 1) & 1), ((ntiles - 1) >> 1) & 1);
-      tc_fence_after();
-    }
+    drain_dq(ntiles - 1);                                           // also: every dV / dK product has completed
     uint32_t r16[16];
-    if (half == 0) {                                                // first warp of the pair: dK; second: dV
-      bf16* pk_ = dk + ((long long)b * N + k0 + row) * lddk + head * D;
-      tmem_ld16(trow + C_DK, r16);
-      if (D == 8) {
-        *reinterpret_cast<uint4*>(pk_) = make_uint4(pack_bf16(__uint_as_float(r16[0]) * scale, __uint_as_float(r16[1]) * scale),
-                                                    pack_bf16(__uint_as_float(r16[2]) * scale, __uint_as_float(r16[3]) * scale),
-                                                    pack_bf16(__uint_as_float(r16[4]) * scale, __uint_as_float(r16[5]) * scale),
-                                                    pack_bf16(__uint_as_float(r16[6]) * scale, __uint_as_float(r16[7]) * scale));
-      } else {
-        *reinterpret_cast<uint2*>(pk_) = make_uint2(pack_bf16(__uint_as_float(head ? r16[4] : r16[0]) * scale, __uint_as_float(head ? r16[5] : r16[1]) * scale),
-                                                    pack_bf16(__uint_as_float(head ? r16[6] : r16[2]) * scale, __uint_as_float(head ? r16[7] : r16[3]) * scale));
-      }
+    bf16* pk_ = dk + ((long long)b * N + k0 + row) * lddk + head * D;
+    bf16* pv_ = dv + ((long long)b * N + k0 + row) * lddv + head * D;
+    tmem_ld16(trow + C_DK, r16);
+    if (D == 8) {
+      *reinterpret_cast<uint4*>(pk_) = make_uint4(pack_bf16(__uint_as_float(r16[0]) * scale, __uint_as_float(r16[1]) * scale),
+                                                  pack_bf16(__uint_as_float(r16[2]) * scale, __uint_as_float(r16[3]) * scale),
+                                                  pack_bf16(__uint_as_float(r16[4]) * scale, __uint_as_float(r16[5]) * scale),
+                                                  pack_bf16(__uint_as_float(r16[6]) * scale, __uint_as_float(r16[7]) * scale));
     } else {
-      bf16* pv_ = dv + ((long long)b * N + k0 + row) * lddv + head * D;
-      tmem_ld16(trow + C_DV, r16);
-      if (D == 8) {
-        *reinterpret_cast<uint4*>(pv_) = make_uint4(pack_bf16(__uint_as_float(r16[0]), __uint_as_float(r16[1])),
-                                                    pack_bf16(__uint_as_float(r16[2]), __uint_as_float(r16[3])),
-                                                    pack_bf16(__uint_as_float(r16[4]), __uint_as_float(r16[5])),
-                                                    pack_bf16(__uint_as_float(r16[6]), __uint_as_float(r16[7])));
-      } else {
-        *reinterpret_cast<uint2*>(pv_) = make_uint2(pack_bf16(__uint_as_float(head ? r16[4] : r16[0]), __uint_as_float(head ? r16[5] : r16[1])),
-                                                    pack_bf16(__uint_as_float(head ? r16[6] : r16[2]), __uint_as_float(head ? r16[7] : r16[3])));
-      }
+      *reinterpret_cast<uint2*>(pk_) = make_uint2(pack_bf16(__uint_as_float(head ? r16[4] : r16[0]) * scale, __uint_as_float(head ? r16[5] : r16[1]) * scale),
+                                                  pack_bf16(__uint_as_float(head ? r16[6] : r16[2]) * scale, __uint_as_float(head ? r16[7] : r16[3]) * scale));
+    }
+    tmem_ld16(trow + C_DV, r16);
+    if (D == 8) {
+      *reinterpret_cast<uint4*>(pv_) = make_uint4(pack_bf16(__uint_as_float(r16[0]), __uint_as_float(r16[1])),
+                                                  pack_bf16(__uint_as_float(r16[2]), __uint_as_float(r16[3])),
+                                                  pack_bf16(__uint_as_float(r16[4]), __uint_as_float(r16[5])),
+                                                  pack_bf16(__uint_as_float(r16[6]), __uint_as_float(r16[7])));
+    } else {
+      *reinterpret_cast<uint2*>(pv_) = make_uint2(pack_bf16(__uint_as_float(head ? r16[4] : r16[0]), __uint_as_float(head ? r16[5] : r16[1])),
+                                                  pack_bf16(__uint_as_float(head ? r16[6] : r16[2]), __uint_as_float(head ? r16[7] : r16[3])));
     }
   }
   tc_fence_before();

@@ -639,14 +639,8 @@ int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b
 }
 
 // ---- halo variant host side ------------------------------------------------------------------------
-int env_int(const char* name, int dflt) {
-  const char* e = getenv(name);
-  return e ? atoi(e) : dflt;
-}
 bool halo_ok(const HnConv* d) {
-  static int enabled = -1;
-  if (enabled < 0) enabled = env_int("HN_TC_HALO", 1);
-  if (!enabled || !tc_ok(d)) return false;
+  if (!tc_ok(d)) return false;
   if (d->stride != 1 || d->pshuf || d->KH != 3 || d->KW != 3 || d->pad != d->dil || d->dil > 4) return false;
   if (d->W % 128) return false;
   const int bkc = pick_bkc(d);
@@ -671,8 +665,9 @@ int launch_halo(const HnConv* d, const void* x1, const void* x2, const void* wpa
     if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "conv_tc_halo: smem attribute: %s", cudaGetErrorString(e));
     configured = true;
   }
-  static int base_off = -1;
-  if (base_off < 0) base_off = env_int("HN_TC_BASEOFF", 0);
+  // descriptors of the row-shifted taps keep base_offset = 0: the swizzle XOR follows the absolute smem address bits
+  // (measured, scripts/check_halo.py)
+  const int base_off = 0;
   // A boxes: {BKC channels, 128 + 2*pad pixels of one row}
   CUtensorMap a1, a2, bm;
   TileGeom g; g.BW = rows; g.BH = 1; g.BB = 1;

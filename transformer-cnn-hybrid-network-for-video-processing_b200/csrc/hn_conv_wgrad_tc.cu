@@ -380,9 +380,7 @@ static int wg_plan(const HnConv* d, const PGeom& g, WgTc* pp) {
   const int jobs = p.mblocks * (p.ct1 + p.ct2) * p.tgroups;
   // one wave of 148 CTAs (one CTA per SM: 512 TMEM columns; measured: a second wave only doubles the
   // flush atomics): the largest split count that keeps jobs * splits <= 148, >= 8 pixel tiles per item
-  static int waves = 0;
-  if (waves == 0) { const char* e = getenv("HN_WG_WAVES"); waves = e ? atoi(e) : 1; if (waves < 1) waves = 1; }
-  int splits = (148 * waves) / jobs;
+  int splits = 148 / jobs;
   int max_splits = p.ptiles / 8 > 0 ? p.ptiles / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
