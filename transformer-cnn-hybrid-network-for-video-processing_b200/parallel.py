@@ -14,6 +14,7 @@ import torch.distributed as dist
 
 class GradArena:
     def __init__(self, model, used=None, buckets=4, process_group=None):
+        self.names = [n for n, p in model.named_parameters() if p.requires_grad and (used is None or n in used)]
         self.params = [p for n, p in model.named_parameters()
                        if p.requires_grad and (used is None or n in used)]
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
@@ -61,6 +62,7 @@ class GradArena:
         self.scale_in_finish = True   # optim.AdamW folds the 1/world into its update and clears this
         self._written = set()         # parameters whose gradient a kernel already reduced into the arena this step
         self._counted = set()         # parameters already counted towards their bucket this step
+        self._rewritten = set()       # sunk parameters that were asked for a second time this step (scratch + autograd)
         self._attach()
         self._hooks = [self._make_hook(i) for i in range(len(self.params))]
         if self.world > 1:
@@ -89,7 +91,10 @@ class GradArena:
             # in the same step (gradient accumulation over micro-batches, a second backward, a module applied
             # twice) therefore gets None: that call reduces into scratch and autograd accumulates it.
             i = self._by_ptr.get(ptr)
-            if i is None or i in self._written:
+            if i is None:
+                return None
+            if i in self._written:
+                self._rewritten.add(i)
                 return None
             s, e = self.slices[i]
             if e - s != numel:
@@ -117,18 +122,26 @@ class GradArena:
         self.works = []
         self._written.clear()
         self._counted.clear()
+        self._rewritten.clear()
 
     def _make_hook(self, i):
         def hook(_p):
             if not self.exchange:
                 return
-            if i in self._counted:
-                # a second gradient for the same parameter after its bucket may already be in flight: the
-                # all-reduce would miss it.  Accumulate micro-batches with ``exchange = False`` and switch it on
-                # for the last one (DDP's no_sync), or call zero_grad() between backward passes.
-                raise RuntimeError("hybridnet.GradArena: parameter received a second gradient in one exchanged step")
-            self._counted.add(i)
             b = self.bucket_of[i]
+            if i in self._counted:
+                # Counted once per parameter per step.  autograd's AccumulateGrad node runs its post hooks even when the
+                # Function returned None for a parameter whose gradient a kernel already reduced into the arena, so
+                # every sunk parameter is notified twice (sink ``done`` first, the engine later): the repeat is
+                # ignored.  A REAL further gradient (micro-batch accumulation, a module applied twice) is harmless while
+                # the bucket has not been sent; once its all-reduce is in flight the sum would miss it: accumulate with
+                # ``exchange = False`` and switch it on for the last micro-batch (DDP's no_sync).
+                benign = _p is not None and i in self._written and i not in self._rewritten
+                if not benign and self.pending[b] == 0:
+                    raise RuntimeError(f"hybridnet.GradArena: parameter {self.names[i]} received a gradient after its "
+                                       "bucket was all-reduced")
+                return
+            self._counted.add(i)
             self.pending[b] -= 1
             if self.pending[b] == 0:
                 self._launch(b)
