@@ -552,12 +552,13 @@ def make_config(args, workload, B, world):
            "parallelism": f"dp{world}" if world > 1 else "single",
            "step": "eval forward" if args.infer else "zero_grad, forward, loss, backward, gradient all-reduce (N>1), AdamW",
            "l2": "activations per step >> 126 MB L2 (no flush needed)"}
-    if workload == "fct" and B % CLIP_FRAMES == 0:
-        cfg["clips"] = {"frames_per_clip": CLIP_FRAMES, "clips_per_gpu": B // CLIP_FRAMES,
-                        "sharding": "one clip split by frame across the ranks" if args.strong_clips else "whole clips per rank"}
-    elif workload == "fct" and args.strong_clips:
+    if workload == "fct" and args.strong_clips:
+        cfg["workload"] = (f"FCT conv-attention net, {args.strong_clips} x {CLIP_FRAMES}-frame clip(s) in total split by frame "
+                           f"across the ranks ({B} frames per GPU), fwd+bwd (BASELINE configs[4])")
         cfg["clips"] = {"frames_per_clip": CLIP_FRAMES, "clips_total": args.strong_clips,
                         "sharding": f"{args.strong_clips} clip(s) split by frame across the ranks: {B} frames per rank"}
+    elif workload == "fct" and B % CLIP_FRAMES == 0:
+        cfg["clips"] = {"frames_per_clip": CLIP_FRAMES, "clips_per_gpu": B // CLIP_FRAMES, "sharding": "whole clips per rank"}
     return cfg
 
 

@@ -74,8 +74,12 @@ if __name__ == "__main__":
     ap.add_argument("--poly", type=int, default=-1)
     ap.add_argument("--tc", type=int, default=-1, help="tcgen05 forward with this polynomial share (0, 2, 3, 4)")
     ap.add_argument("--tcbwd", action="store_true", help="tcgen05 backward as well (with --tc)")
+    ap.add_argument("--lib", default="", help="a variant library built by scripts/attn_variants.sh")
+    ap.add_argument("--big-only", action="store_true", help="only the two exponential-bound shapes")
     a = ap.parse_args()
-    ap.add_argument  # noqa
+    if a.lib:
+        _lib.LIB_PATH = os.path.abspath(a.lib)
+        print("library:", a.lib)
     if a.tc >= 0:
         TC["on"], TC["poly"], TC["bwd"] = True, a.tc, a.tcbwd
         print("tcgen05 forward, polynomial share: every", a.tc)
@@ -86,7 +90,8 @@ if __name__ == "__main__":
         call("hn_attn_tune", a.kb)
         print("fused backward keys per CTA:", a.kb)
     tot = {"fwd": 0.0, "bwd": 0.0}
-    for N, D, mult in ((16384, 4, 2), (4096, 8, 2), (1024, 16, 2), (256, 32, 2), (64, 64, 1)):
+    shapes = ((16384, 4, 2), (4096, 8, 2), (1024, 16, 2), (256, 32, 2), (64, 64, 1))
+    for N, D, mult in (shapes[:2] if a.big_only else shapes):
         r = run(32, N, 2, D)
         for kk in tot:
             tot[kk] += mult * r[kk]

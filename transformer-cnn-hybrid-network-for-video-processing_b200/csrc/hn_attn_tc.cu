@@ -11,9 +11,9 @@
 //           descriptors' leading byte offset; for D = 4 both heads share one 16-byte row, so Q is staged with the other
 //           head's channels zeroed.  N of the second product is 16: the 8 V channels and a panel of ones, so the tensor
 //           core also delivers the softmax row sum (output column 8) from the same bf16-rounded probabilities.
-//   warps 2-5  softmax, one thread per query row (TMEM lane): tcgen05.ld S -> running max (lazy: the reference max only
-//           moves when the tile max exceeds it by 2^8, then O is rescaled in TMEM) -> exp2 -> bf16 pairs -> tcgen05.st P
-//           over the S columns it just consumed.
+//   warps 2-5  softmax, one thread per query row (TMEM lane), ONE pass over S per tile: tcgen05.ld S -> exp2 against the
+//           reference maximum of the tiles before (the tile's own maximum is collected beside it; the reference only moves
+//           when a tile exceeds it by 2^8: then O is rescaled in TMEM and the tile redone) -> bf16 pairs -> tcgen05.st P.
 //   The MUFU unit (16 exp2 / clk / SM) binds this kernel, exactly as it binds the mma.sync form; what tcgen05 removes
 //   from the SM's issue slots is the MMA / ldmatrix / fragment traffic (5.6 -> ~3 instructions per score element), which is
 //   what makes room for taking part of the exponentials on the FMA pipe (ex2_poly2).
@@ -304,45 +304,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
       tc_fence_after();
       uint32_t ra[32], rb[32];
       float m_tile = -INFINITY;
-      // pass 1: row maximum; the load of chunk c + 1 is in flight while chunk c is reduced
-      tmem_ld32_nowait(trow, ra);
-#pragma unroll
-      for (int c = 0; c < TK / 32; ++c) {
-        uint32_t* cur = (c & 1) ? rb : ra;
-        uint32_t* nxt = (c & 1) ? ra : rb;
-        tmem_ld_wait32(cur);
-        if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
-        else tmem_ld32_nowait(trow, nxt);                          // chunk 0 again, for pass 2
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
-      }
-      // the previous tile's P V must be done before its P columns are overwritten / O is rescaled
-      if (j > 0) {
-        mbar_wait(kv_empty + 8 * ((j - 1) % NST), ((j - 1) / NST) & 1);
-        tc_fence_after();
-      }
-      // lazy rescale: move the reference only when this tile exceeds it by more than 2^8 (probabilities stay < 256)
-      const bool need = (m_tile - m_ref) * sl2 > 8.f;
-      if (__any_sync(0xffffffffu, need)) {
-        if (j > 0) {
-          const float alpha = need ? ex2((m_ref - m_tile) * sl2) : 1.f;
-          uint32_t ov[16];
-          tmem_ld16(trow + COL_O, ov);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
-          tmem_st16(trow + COL_O, ov);
-        }
-        if (need) m_ref = m_tile;
-      }
-      const float moff = -m_ref * sl2;
-      // pass 2 (chunk 0 was requested into ra/rb above: TK / 32 is even, so it sits in ra)
-#pragma unroll
-      for (int c = 0; c < TK / 32; ++c) {
-        uint32_t* cur = (c & 1) ? rb : ra;
-        uint32_t* nxt = (c & 1) ? ra : rb;
-        tmem_ld_wait32(cur);
-        if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
-        uint32_t pk[16];
+      // exponentials of one 32-column chunk against the reference maximum folded into `moff`
+      auto exp_chunk = [&](const uint32_t* cur, float moff, uint32_t* pk) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float x0, x1;
@@ -355,7 +318,67 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
           }
           pk[i] = pack_bf16(x0, x1);
         }
-        tmem_st16(trow + COL_P + c * 16, pk);
+      };
+      tmem_ld32_nowait(trow, ra);
+      if (j == 0) {
+        // first tile: there is no reference yet -- row maximum only, the exponentials follow in the block below
+#pragma unroll
+        for (int c = 0; c < TK / 32; ++c) {
+          uint32_t* cur = (c & 1) ? rb : ra;
+          uint32_t* nxt = (c & 1) ? ra : rb;
+          tmem_ld_wait32(cur);
+          if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+        }
+      } else {
+        // ONE pass, optimistic: the exponentials are taken against the reference of the tiles before while the row
+        // maximum of this tile is collected on the side (FMNMX3 on the ALU pipe, under the MUFU-bound stream).  The
+        // reference only has to move when a tile exceeds it by more than 2^8 -- after the first tiles of a sweep that is
+        // rare -- and then the tile is simply redone below (S is still in TMEM: S(j + 1) is issued after p_full(j)).
+        const float moff = -m_ref * sl2;
+#pragma unroll
+        for (int c = 0; c < TK / 32; ++c) {
+          uint32_t* cur = (c & 1) ? rb : ra;
+          uint32_t* nxt = (c & 1) ? ra : rb;
+          tmem_ld_wait32(cur);
+          if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+          uint32_t pk[16];
+          exp_chunk(cur, moff, pk);
+          if (c == 0) {      // the previous tile's P V must be done before its P columns are overwritten / O is rescaled
+            mbar_wait(kv_empty + 8 * ((j - 1) % NST), ((j - 1) / NST) & 1);
+            tc_fence_after();
+          }
+          tmem_st16(trow + COL_P + c * 16, pk);
+        }
+      }
+      // lazy rescale: move the reference only when this tile exceeds it by more than 2^8 (probabilities stay < 256)
+      const bool need = (m_tile - m_ref) * sl2 > 8.f;
+      if (__any_sync(0xffffffffu, need)) {
+        if (j > 0) {
+          const float alpha = need ? ex2((m_ref - m_tile) * sl2) : 1.f;
+          uint32_t ov[16];
+          tmem_st_wait();
+          tmem_ld16(trow + COL_O, ov);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+          tmem_st16(trow + COL_O, ov);
+        }
+        if (need) m_ref = m_tile;
+        const float moff = -m_ref * sl2;
+        tmem_ld32_nowait(trow, ra);
+#pragma unroll
+        for (int c = 0; c < TK / 32; ++c) {
+          uint32_t* cur = (c & 1) ? rb : ra;
+          uint32_t* nxt = (c & 1) ? ra : rb;
+          tmem_ld_wait32(cur);
+          if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
+          uint32_t pk[16];
+          exp_chunk(cur, moff, pk);
+          tmem_st16(trow + COL_P + c * 16, pk);
+        }
       }
       tmem_st_wait();
       tc_fence_before();
