@@ -196,7 +196,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
                    const bf16* __restrict__ q, bf16* __restrict__ o, float* __restrict__ lse, int N, int heads, int ldq,
                    int ldo, float scale) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t bars[2 * NST + 3];
+  __shared__ __align__(8) uint64_t bars[2 * NST + 4];
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.y, b = blockIdx.z;
@@ -205,12 +205,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
   const uint32_t sbase = smem_u32(smem);
   const uint32_t kv_full = smem_u32(&bars[0]), kv_empty = smem_u32(&bars[NST]);
   const uint32_t s_full = smem_u32(&bars[2 * NST]), p_full = smem_u32(&bars[2 * NST + 1]), o_full = smem_u32(&bars[2 * NST + 2]);
+  const uint32_t s_free = smem_u32(&bars[2 * NST + 3]);      // every softmax warp holds the last S columns in registers
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) { mbar_init(kv_full + 8 * s, 1); mbar_init(kv_empty + 8 * s, 1); }
     mbar_init(s_full, 1);
     mbar_init(p_full, 4);
     mbar_init(o_full, 1);
+    mbar_init(s_free, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -267,11 +269,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
     for (int j = 0; j < ntiles; ++j) {
       const int st = j % NST;
       const uint32_t vp = sbase + OFF_KV + st * 2 * PANEL + PANEL;
-      mbar_wait(p_full, j & 1);
-      tc_fence_after();
       if (j + 1 < ntiles) {
+        // S(j + 1) as soon as the softmax warps hold the last columns of S(j) in registers (a quarter of the tile's
+        // exponentials is still to come): the tensor-core round trip hides behind them
         const int sn = (j + 1) % NST;
         mbar_wait(kv_full + 8 * sn, ((j + 1) / NST) & 1);
+        mbar_wait(s_free, j & 1);
         tc_fence_after();
         if (leader) {
           const uint32_t kp = sbase + OFF_KV + sn * 2 * PANEL;
@@ -280,6 +283,8 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
         }
         __syncwarp();
       }
+      mbar_wait(p_full, j & 1);
+      tc_fence_after();
       if (leader) {
 #pragma unroll
         for (int ks = 0; ks < TK / 16; ++ks) {
@@ -304,6 +309,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
       tc_fence_after();
       uint32_t ra[32], rb[32];
       float m_tile = -INFINITY;
+      bool redo = true;                        // tile 0 always takes the block below
       // exponentials of one 32-column chunk against the reference maximum folded into `moff`
       auto exp_chunk = [&](const uint32_t* cur, float moff, uint32_t* pk) {
 #pragma unroll
@@ -345,6 +351,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
           if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
 #pragma unroll
           for (int i = 0; i < 32; i += 2) m_tile = max3(m_tile, __uint_as_float(cur[i]), __uint_as_float(cur[i + 1]));
+          if (c == TK / 32 - 1) {
+            // all of S(j) is in registers and the tile maximum is known: unless the tile has to be redone its columns are
+            // free for S(j + 1) (bare arrive: tcgen05.wait::ld has completed the loads)
+            redo = __any_sync(0xffffffffu, (m_tile - m_ref) * sl2 > 8.f);
+            if (!redo && lane == 0 && j + 1 < ntiles) mbar_arrive(s_free);
+          }
           uint32_t pk[16];
           exp_chunk(cur, moff, pk);
           if (c == 0) {      // the previous tile's P V must be done before its P columns are overwritten / O is rescaled
@@ -356,7 +368,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
       }
       // lazy rescale: move the reference only when this tile exceeds it by more than 2^8 (probabilities stay < 256)
       const bool need = (m_tile - m_ref) * sl2 > 8.f;
-      if (__any_sync(0xffffffffu, need)) {
+      if (redo) {
         if (j > 0) {
           const float alpha = need ? ex2((m_ref - m_tile) * sl2) : 1.f;
           uint32_t ov[16];
@@ -375,6 +387,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap mapK, const __grid_consta
           uint32_t* nxt = (c & 1) ? ra : rb;
           tmem_ld_wait32(cur);
           if (c + 1 < TK / 32) tmem_ld32_nowait(trow + (c + 1) * 32, nxt);
+          else if (lane == 0 && j + 1 < ntiles) mbar_arrive(s_free);
           uint32_t pk[16];
           exp_chunk(cur, moff, pk);
           tmem_st16(trow + COL_P + c * 16, pk);
