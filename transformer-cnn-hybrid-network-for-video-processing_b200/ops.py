@@ -7,6 +7,7 @@ Cp is the channel count rounded up to 8 (only the RGB input and the 1/3-channel
 heads are actually padded).  A channel slice ``t[..., a:b]`` of such a tensor is
 itself a valid operand (pixel stride = ld), which is how concat costs nothing.
 """
+import contextlib
 import math
 import os
 import weakref
@@ -538,15 +539,42 @@ def _s2dgrad_ok(g, dz):
     return bool(_lib.load().hn_conv_tc_supported(d))
 
 
+# The weight gradient and the input gradient of one layer are independent given dz.  The small layers (FCT: C = 8..64,
+# maps down to 8x8) launch 16..64 CTAs each and leave most of the 148 SMs idle, so the weight gradient goes to a side
+# stream and runs beside the input gradient; the streams join again before the function returns (every tensor the
+# side stream touches is alive until then, and the gradient sink's `done` fires after the join).  Under CapturedStep the
+# fork / join become graph edges.
+WGRAD_OVERLAP = True
+_side_streams = {}
+
+
+def _side_stream(dev):
+    st = _side_streams.get(dev.index)
+    if st is None:
+        st = _side_streams[dev.index] = torch.cuda.Stream(device=dev)
+    return st
+
+
 def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
     """dz: gradient at the conv output (NHWC, padded channels zero). Returns dx1, dx2, dW."""
+    if not (WGRAD_OVERLAP and need_dx and need_dw):
+        return _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, None)
+    dz, _ = nhwc(dz)
+    return _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, _side_stream(dz.device))
+
+
+def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side):
     dx1 = dx2 = dw = None
     dz, _ = nhwc(dz)
     B = x1.shape[0]
     C1 = x1.shape[3]
     C2 = x2.shape[3] if x2 is not None else 0
     sunk = None
-    if need_dw:
+    main = torch.cuda.current_stream() if side is not None else None
+    if side is not None:
+        side.wait_stream(main)
+    with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+      if need_dw:
         sunk = _sink_for(weight)
         dw = sunk.view(weight.shape) if sunk is not None else _f32(tuple(weight.shape), weight)
         if g.transposed:
@@ -587,6 +615,8 @@ def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
                 full = small
             dx1 = full[..., :C1] if C2 else full
             dx2 = full[..., C1:] if C2 else None
+    if side is not None:
+        main.wait_stream(side)
     if sunk is not None:
         _sink_done(weight.data_ptr())
         dw = None
