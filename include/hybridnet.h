@@ -270,6 +270,13 @@ int hn_conv_tc_fwd(const HnConv* d, const void* x1, const void* x2, const void* 
 int hn_conv_sc_supported(const HnConv* d);
 int hn_conv_sc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
                    const float* bias, void* y, float* stat_sum, float* stat_sqsum, void* stream);
+/* the same with the residual epilogue of hn_conv2d_fwd (y = act(conv + bias + res), d->ldr = pixel stride of res): the
+ * Transformer's `conv1(x1) + x` (FCT.py:93-95).  d->ups = 1 (x1 is the H/2 x W/2 map read through nearest-neighbour 2x
+ * upsampling, C2 = 0: Block_decoder's Upsample -> conv, FCT.py:167-172) is accepted by both entry points and by
+ * hn_conv_wgrad_sc. */
+int hn_conv_sc_fwd_res(const HnConv* d, const void* x1, const void* x2, const void* wpacked,
+                       const float* bias, const void* res, void* y, float* stat_sum,
+                       float* stat_sqsum, void* stream);
 
 /* small-channel weight gradient: same contract as hn_conv2d_wgrad for the hn_conv_sc_fwd geometries */
 int hn_conv_wgrad_sc_supported(const HnConv* d);

@@ -205,6 +205,60 @@ def test_conv_virtual_concat_upsample_residual(ops):
     assert rel_l2(s.grad, sr) < BWD_TOL and rel_l2(w2.grad, wr) < BWD_TOL
 
 
+@pytest.mark.parametrize("C,k", [(8, 3), (16, 3), (32, 1), (32, 3)])
+def test_small_channel_conv_residual_and_upsample(ops, C, k):
+    """The small-channel kernels (hn_conv_sc_fwd_res, hn_conv_wgrad_sc) with the residual epilogue (Transformer:
+    conv1(x1) + x, FCT.py:93-95) and with the nearest-x2 upsample folded into the halo gather (Block_decoder,
+    FCT.py:167-172): maps with H % 16 == 0 and W % 32 == 0 take that path."""
+    from hybridnet import _lib
+    B, H, W = 2, 32, 64
+    x = _rand(B, C, H, W, seed=1).requires_grad_(True)
+    w = _rand(C, C, k, k, seed=3, scale=0.5 / math.sqrt(C * k * k)).requires_grad_(True)
+    bias = _rand(C, seed=4, scale=0.1).requires_grad_(True)
+    res = _rand(B, C, H, W, seed=6).requires_grad_(True)
+    ref = F.conv2d(x, w, bias, 1, k // 2) + res
+    gy = _rand(*ref.shape, seed=5)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (x, w, bias, res)]
+    for t in (x, w, bias, res):
+        t.grad = None
+    import contextlib
+    names = []
+
+    @contextlib.contextmanager
+    def record(name, args):
+        names.append(name)
+        yield
+    _lib.set_profiler(record)
+    try:
+        out = ops.to_nchw(ops.conv2d(ops.to_nhwc(x), w, bias, pad=k // 2, res=ops.to_nhwc(res)), C)
+        assert rel_l2(out, ref) < FWD_TOL
+        out.backward(gy)
+    finally:
+        _lib.set_profiler(None)
+    assert "hn_conv_sc_fwd_res" in names and "hn_conv2d_fwd" not in names, names
+    for t, r in zip((x, w, bias, res), want):
+        assert rel_l2(t.grad, r) < BWD_TOL
+
+    s = _rand(B, C, H // 2, W // 2, seed=7).requires_grad_(True)
+    w2 = _rand(C, C, 3, 3, seed=8, scale=0.5 / math.sqrt(C * 9)).requires_grad_(True)
+    ref = F.relu(F.conv2d(F.interpolate(s, scale_factor=2.0, mode="nearest"), w2, None, 1, 1))
+    gy = _rand(*ref.shape, seed=9)
+    ref.backward(gy)
+    sr, wr = s.grad.clone(), w2.grad.clone()
+    s.grad = w2.grad = None
+    names.clear()
+    _lib.set_profiler(record)
+    try:
+        out = ops.to_nchw(ops.conv2d(ops.to_nhwc(s), w2, None, ups=1, act="relu"), C)
+        assert rel_l2(out, ref) < FWD_TOL
+        out.backward(gy)
+    finally:
+        _lib.set_profiler(None)
+    assert "hn_conv_sc_fwd" in names and "hn_conv_wgrad_sc" in names and "hn_conv2d_wgrad" not in names, names
+    assert rel_l2(s.grad, sr) < BWD_TOL and rel_l2(w2.grad, wr) < BWD_TOL
+
+
 @pytest.mark.parametrize("cin,cout", [(64, 32), (512, 256), (256, 384)])
 def test_conv_transpose_k2s2(ops, cin, cout):
     B, H = 2, 8

@@ -85,6 +85,7 @@ SIGNATURES = {
     "hn_conv_tc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
     "hn_conv_sc_supported": [POINTER(HnConv)],
     "hn_conv_sc_fwd": [POINTER(HnConv), _P, _P, _P, _FP, _P, _FP, _FP, _P],
+    "hn_conv_sc_fwd_res": [POINTER(HnConv), _P, _P, _P, _FP, _P, _P, _FP, _FP, _P],
     "hn_conv_wgrad_sc_supported": [POINTER(HnConv)],
     "hn_conv_wgrad_sc": [POINTER(HnConv), _P, _P, _P, _FP, _I, _L, _L, _L, _L, _P],
     "hn_conv_wgrad_tc_supported": [POINTER(HnConv)],

@@ -25,8 +25,9 @@ struct ScP {
   bf16* y;
   float* ssum;
   float* ssq;
+  const bf16* res;                       // optional residual added before the activation (pixel stride ldr)
   int B, H, W, C1, C2, ld1, ld2, ldy, Cout, Kpad;
-  int KH, KW, pad, dil, act;
+  int KH, KW, pad, dil, act, ups, ldr;   // ups: x1 is the H/2 x W/2 map, read through nearest-neighbour 2x upsampling
   int CG, CG1, lgCG, sh;                 // 8-channel chunks (total, from x1), log2, swizzle shift
   int Kc, KS;                            // K chunks = taps*CG, k16 steps
   int wrow;                              // weight row pitch in shared memory (bytes, odd multiple of 16)
@@ -88,7 +89,9 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
       const int r = pc / p.WR, c = pc - r * p.WR;
       const int ih = h0 - p.pad + r, iw = w0 - p.pad + c;
       const bool ok = (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
-      const long long pix = ((long long)b * p.H + (ok ? ih : 0)) * p.W + (ok ? iw : 0);
+      const int sh_ = ok ? ih : 0, sw_ = ok ? iw : 0;
+      const long long pix = p.ups ? ((long long)b * (p.H >> 1) + (sh_ >> 1)) * (p.W >> 1) + (sw_ >> 1)
+                                  : ((long long)b * p.H + sh_) * p.W + sw_;
       const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
       cp_async16(smem_u32(dstb + ((pc << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
     }
@@ -203,7 +206,9 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int ow = w0 + (mt & 1) * 16 + g + h * 8;
-          bf16* dst = p.y + (((long long)b * p.H + oh) * p.W + ow) * p.ldy;
+          const long long opix = ((long long)b * p.H + oh) * p.W + ow;
+          bf16* dst = p.y + opix * p.ldy;
+          const bf16* rsd = p.res ? p.res + opix * p.ldr : nullptr;
 #pragma unroll
           for (int j = 0; j < NT; ++j) {
             const int n = j * 8 + 2 * t;
@@ -212,6 +217,10 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
               const float r0 = bf16_round(v0), r1 = bf16_round(v1);
               csum[j][0] += r0; csq[j][0] += r0 * r0;
               csum[j][1] += r1; csq[j][1] += r1 * r1;
+            }
+            if (rsd) {
+              const float2 rr = __bfloat1622float2(*reinterpret_cast<const bf162*>(rsd + n));
+              v0 += rr.x; v1 += rr.y;
             }
             v0 = n < p.Cout ? apply_act(v0, p.act) : 0.f;
             v1 = n + 1 < p.Cout ? apply_act(v1, p.act) : 0.f;
@@ -260,7 +269,9 @@ int sc_smem_bytes(const HnConv* d, int nbuf) {
   return n8 * wch * 16 + 128 + nbuf * (TH + (d->KH - 1) * d->dil) * (TW + (d->KW - 1) * d->dil) * cg * 16;
 }
 bool sc_ok(const HnConv* d) {
-  if (!d || d->mode != 0 || d->stride != 1 || d->ups != 0 || d->pshuf != 0) return false;
+  if (!d || d->mode != 0 || d->stride != 1 || d->pshuf != 0) return false;
+  if (d->ups && (d->C2 != 0 || (d->H & 1) || (d->W & 1))) return false;
+  if (d->ldr && (d->ldr % 2 || d->ldr < d->Cout)) return false;
   if (d->KH != d->KW || (d->KH != 1 && d->KH != 3) || d->dil < 1 || d->dil > 8) return false;
   if (d->OH != d->H || d->OW != d->W || d->pad != d->dil * (d->KH - 1) / 2) return false;
   if (d->H % TH || d->W % TW) return false;
@@ -304,7 +315,14 @@ extern "C" int hn_conv_sc_supported(const HnConv* d) { return sc_ok(d) ? 1 : 0; 
 
 extern "C" int hn_conv_sc_fwd(const HnConv* d, const void* x1, const void* x2, const void* wpacked, const float* bias,
                               void* y, float* stat_sum, float* stat_sqsum, void* stream) {
+  HN_REQUIRE(d && d->ldr == 0, "conv_sc_fwd: a residual (ldr != 0) needs hn_conv_sc_fwd_res");
+  return hn_conv_sc_fwd_res(d, x1, x2, wpacked, bias, nullptr, y, stat_sum, stat_sqsum, stream);
+}
+
+extern "C" int hn_conv_sc_fwd_res(const HnConv* d, const void* x1, const void* x2, const void* wpacked, const float* bias,
+                                  const void* res, void* y, float* stat_sum, float* stat_sqsum, void* stream) {
   HN_REQUIRE(sc_ok(d), "conv_sc_fwd: geometry not supported by the small-channel path (use hn_conv2d_fwd)");
+  HN_REQUIRE((res != nullptr) == (d->ldr != 0) && ((uintptr_t)res % 4) == 0, "conv_sc_fwd: residual pointer and ldr must come together");
   HN_REQUIRE(x1 && wpacked && y && (d->C2 == 0 || x2), "conv_sc_fwd: null pointer");
   HN_REQUIRE((stat_sum == nullptr) == (stat_sqsum == nullptr), "conv_sc_fwd: stats need both buffers");
   HN_REQUIRE(((uintptr_t)x1 % 16) == 0 && ((uintptr_t)wpacked % 16) == 0 && ((uintptr_t)y % 4) == 0 && ((uintptr_t)x2 % 16) == 0,
@@ -312,6 +330,7 @@ extern "C" int hn_conv_sc_fwd(const HnConv* d, const void* x1, const void* x2, c
   ScP p;
   p.x1 = (const bf16*)x1; p.x2 = (const bf16*)x2; p.w = (const bf16*)wpacked; p.bias = bias; p.y = (bf16*)y;
   p.ssum = stat_sum; p.ssq = stat_sqsum;
+  p.res = (const bf16*)res; p.ups = d->ups; p.ldr = d->ldr;
   p.B = d->B; p.H = d->H; p.W = d->W; p.C1 = d->C1; p.C2 = d->C2; p.ld1 = d->ld1; p.ld2 = d->ld2; p.ldy = d->ldy;
   p.Cout = d->Cout; p.Kpad = d->Kpad; p.KH = d->KH; p.KW = d->KW; p.pad = d->pad; p.dil = d->dil; p.act = d->act;
   const int cin = d->C1 + d->C2;

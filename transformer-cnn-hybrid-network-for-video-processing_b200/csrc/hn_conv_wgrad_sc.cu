@@ -20,7 +20,7 @@ struct WsP {
   const bf16* dz;
   float* dw;
   int B, H, W, C1, C2, ld1, ld2, lddz, Cout, Creal;
-  int KH, KW, pad, dil;
+  int KH, KW, pad, dil, ups;             // ups: x1 is the H/2 x W/2 map read through nearest-neighbour 2x upsampling
   int CG, CG1, lgCG, sh;                 // input 8-channel chunks
   int NC, lgNC, shn;                     // dz 8-channel chunks
   int Kc;                                // taps * CG
@@ -76,7 +76,9 @@ __global__ void __launch_bounds__(WS_THREADS) wgrad_sc_kernel(const WsP p) {
       const int r = pc / p.WR, c = pc - r * p.WR;
       const int ih = h0 - p.pad + r, iw = w0 - p.pad + c;
       const bool ok = (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
-      const long long pix = ((long long)b * p.H + (ok ? ih : 0)) * p.W + (ok ? iw : 0);
+      const int sh_ = ok ? ih : 0, sw_ = ok ? iw : 0;
+      const long long pix = p.ups ? ((long long)b * (p.H >> 1) + (sh_ >> 1)) * (p.W >> 1) + (sw_ >> 1)
+                                  : ((long long)b * p.H + sh_) * p.W + sw_;
       const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
       cp_async16(smem_u32(sH + ((pc << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
     }
@@ -156,7 +158,8 @@ int ws_smem_bytes(const HnConv* d) {
   return (TH + (d->KH - 1) * d->dil) * (TW + (d->KW - 1) * d->dil) * cg * 16 + TH * TW * n8 * 2;
 }
 bool ws_ok(const HnConv* d) {
-  if (!d || d->mode != 0 || d->stride != 1 || d->ups != 0 || d->pshuf != 0) return false;
+  if (!d || d->mode != 0 || d->stride != 1 || d->pshuf != 0) return false;
+  if (d->ups && (d->C2 != 0 || (d->H & 1) || (d->W & 1))) return false;
   if (d->KH != d->KW || (d->KH != 1 && d->KH != 3) || d->dil < 1 || d->dil > 8) return false;
   if (d->OH != d->H || d->OW != d->W || d->pad != d->dil * (d->KH - 1) / 2) return false;
   if (d->H % TH || d->W % TW) return false;
@@ -214,7 +217,7 @@ extern "C" int hn_conv_wgrad_sc(const HnConv* d, const void* x1, const void* x2,
   WsP p;
   p.x1 = (const bf16*)x1; p.x2 = (const bf16*)x2; p.dz = (const bf16*)dy; p.dw = dw;
   p.B = d->B; p.H = d->H; p.W = d->W; p.C1 = d->C1; p.C2 = d->C2; p.ld1 = d->ld1; p.ld2 = d->ld2; p.lddz = d->ldy;
-  p.Cout = d->Cout; p.Creal = Creal; p.KH = d->KH; p.KW = d->KW; p.pad = d->pad; p.dil = d->dil;
+  p.Cout = d->Cout; p.Creal = Creal; p.KH = d->KH; p.KW = d->KW; p.pad = d->pad; p.dil = d->dil; p.ups = d->ups;
   const int cin = d->C1 + d->C2;
   p.CG = cin / 8; p.CG1 = d->C1 / 8;
   p.lgCG = p.CG == 1 ? 0 : (p.CG == 2 ? 1 : (p.CG == 4 ? 2 : 3));

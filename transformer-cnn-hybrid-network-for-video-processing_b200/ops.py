@@ -408,9 +408,13 @@ def _conv_raw(x1, x2, wp, Kpad, bias, res, *, OH, OW, Cout, KH, KW, stride, pad,
         call("hn_conv_tc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
              _ptr(s1), _stream())
         return out
-    if res is None and USE_SC and _lib.load().hn_conv_sc_supported(d):
-        call("hn_conv_sc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
-             _ptr(s1), _stream())
+    if USE_SC and _lib.load().hn_conv_sc_supported(d):
+        if res is None:
+            call("hn_conv_sc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
+                 _ptr(s1), _stream())
+        else:
+            call("hn_conv_sc_fwd_res", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), res.data_ptr(),
+                 out.data_ptr(), _ptr(s0), _ptr(s1), _stream())
         return out
     if res is None and USE_TC and _lib.load().hn_conv_tc_supported(d):
         call("hn_conv_tc_fwd", d, x1.data_ptr(), _ptr(x2), wp.data_ptr(), _ptr(bias), out.data_ptr(), _ptr(s0),
