@@ -234,6 +234,16 @@ int hn_attn_bwd_tc(const void* q, const void* k, const void* v, const void* o, c
                    float* workspace, long long workspace_floats, void* dq, void* dk, void* dv, int B, int N, int heads,
                    int D, int ldq, int ldk, int ldv, int ldo, int lddo, int lddq, int lddk, int lddv, float scale,
                    int poly_every, void* stream);
+/* hn_attn_bwd_tc without a caller workspace: the scratch (auxiliary panels + fp32 dQ accumulator) is a file-scope device
+ * array of HN_ATTN_BWD_TC_STATIC_MAX_FLOATS fp32 (8 MiB, resident on every GPU that loads the library), so the call
+ * allocates nothing: for code under CUDA graph capture, serving loops and harnesses that forbid cudaMalloc.  No
+ * counterpart in the reference.  Shapes as hn_attn_bwd_tc, with
+ * B * N * (16 + 2 D) <= HN_ATTN_BWD_TC_STATIC_MAX_FLOATS (e.g. B = 4, N = 16384, D = 8); larger sizes are rejected with
+ * HN_EINVAL.  Every call shares the array (the entry point re-initialises what it needs): calls that overlap on the GPU race. */
+#define HN_ATTN_BWD_TC_STATIC_MAX_FLOATS (2 * 1024 * 1024)
+int hn_attn_bwd_tc_static(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
+                          void* dq, void* dk, void* dv, int B, int N, int heads, int D, int ldq, int ldk, int ldv,
+                          int ldo, int lddo, int lddq, int lddk, int lddv, float scale, int poly_every, void* stream);
 /* forward, D <= 8: every poly_every-th 8-key tile computes exp2 on the FMA pipe (polynomial) instead of MUFU;
  * 0 = never, default 4; process-wide */
 int hn_attn_tune_fwd(int poly_every);

@@ -75,6 +75,7 @@ SIGNATURES = {
     "hn_attn_bwd_tc_workspace": [_I, _I, _I, _I],
     "hn_attn_bwd_tc_supported": [_I, _I, _I, _I, _I, _I, _I, _I, _I, _I],
     "hn_attn_bwd_tc": [_P, _P, _P, _P, _P, _FP, _FP, _L, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _I, _P],
+    "hn_attn_bwd_tc_static": [_P, _P, _P, _P, _P, _FP, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _I, _P],
     "hn_attn_fwd_tc_supported": [_I, _I, _I, _I, _I, _I],
     "hn_attn_fwd_tc": [_P, _P, _P, _P, _FP, _I, _I, _I, _I, _I, _I, _I, _I, _F, _I, _P],
     "hn_attn_tune_fwd": [_I],
@@ -128,7 +129,7 @@ def load():
 
 
 # kernels launched per entry point (for the launch count bench.py reports)
-LAUNCHES = {"hn_attn_bwd": 3, "hn_attn_bwd_tc": 3}
+LAUNCHES = {"hn_attn_bwd": 3, "hn_attn_bwd_tc": 3, "hn_attn_bwd_tc_static": 3}
 stats = {"calls": 0, "launches": 0}
 _profiler = None      # optional callable(name, args) -> context manager (bench.py roofline pass)
 

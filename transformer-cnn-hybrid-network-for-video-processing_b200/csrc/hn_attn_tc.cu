@@ -872,3 +872,48 @@ extern "C" int hn_attn_bwd_tc(const void* q, const void* k, const void* v, const
   HN_CHECK_LAUNCH("attn_dq_cast_tc");
   return HN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// hn_attn_bwd_tc with its workspace (auxiliary panels + the fp32 dQ accumulator) in a file-scope device array instead of
+// caller memory: for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.
+//   * the array is HN_ATTN_BWD_TC_STATIC_MAX_FLOATS fp32 = 8 MiB, held by every GPU that loads the library until exit;
+//   * in HOST code `g_attn_bwd_scratch` is only a stand-in symbol, not a device address: the address comes from
+//     cudaGetSymbolAddress, once per device, with that device current;
+//   * every call shares the array and finds the previous call's contents in it: the entry point rewrites the auxiliary
+//     panels and clears the dQ accumulator itself; calls that overlap on the GPU (two streams, two host threads) race.
+static __device__ __align__(256) float g_attn_bwd_scratch[HN_ATTN_BWD_TC_STATIC_MAX_FLOATS];
+
+static int attn_bwd_scratch_ptr(float** out) {
+  constexpr int MAXDEV = 64;
+  static float* ptrs[MAXDEV] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "attn_bwd_tc_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  HN_REQUIRE(dev >= 0 && dev < MAXDEV, "attn_bwd_tc_static: device index %d out of range", dev);
+  if (!ptrs[dev]) {
+    float* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_attn_bwd_scratch);
+    if (e != cudaSuccess || !ptr) HN_FAIL(HN_ECUDA, "attn_bwd_tc_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    ptrs[dev] = ptr;
+  }
+  *out = ptrs[dev];
+  return HN_OK;
+}
+
+extern "C" int hn_attn_bwd_tc_static(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                                     const float* lse, void* dq, void* dk, void* dv, int B, int N, int heads, int D, int ldq,
+                                     int ldk, int ldv, int ldo, int lddo, int lddq, int lddk, int lddv, float scale,
+                                     int poly_every, void* stream) {
+  HN_REQUIRE(B > 0 && N > 0 && heads == 2 && (D == 4 || D == 8), "attn_bwd_tc_static: bad args");
+  const long long need = hn_attn_bwd_tc_workspace(B, N, heads, D);
+  HN_REQUIRE(need <= (long long)HN_ATTN_BWD_TC_STATIC_MAX_FLOATS,
+             "attn_bwd_tc_static: B = %d, N = %d, D = %d needs %lld fp32 of scratch, the built-in array holds %lld "
+             "(B * N * (16 + 2 D) <= %lld): use hn_attn_bwd_tc with a caller workspace",
+             B, N, D, need, (long long)HN_ATTN_BWD_TC_STATIC_MAX_FLOATS, (long long)HN_ATTN_BWD_TC_STATIC_MAX_FLOATS);
+  float* ws = nullptr;
+  if (int rc = attn_bwd_scratch_ptr(&ws)) return rc;
+  // hn_attn_bwd_tc rewrites the panels for these inputs and clears the accumulator (cudaMemsetAsync) before the kernel
+  return hn_attn_bwd_tc(q, k, v, o, dout, lse, ws, (long long)HN_ATTN_BWD_TC_STATIC_MAX_FLOATS, dq, dk, dv, B, N, heads, D, ldq, ldk,
+                        ldv, ldo, lddo, lddq, lddk, lddv, scale, poly_every, stream);
+}
