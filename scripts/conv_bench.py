@@ -43,7 +43,11 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--wgrad", action="store_true")
     ap.add_argument("--nostats", action="store_true")
+    ap.add_argument("--lib", default="", help="a variant library built by scripts/attn_variants.sh")
     a = ap.parse_args()
+    if a.lib:
+        _lib.LIB_PATH = os.path.abspath(a.lib)
+        print("library:", a.lib)
     lib = _lib.load()
     dev = torch.device("cuda")
     torch.manual_seed(0)

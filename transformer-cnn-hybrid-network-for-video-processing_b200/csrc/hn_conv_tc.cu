@@ -152,38 +152,96 @@ __device__ __forceinline__ float colsum32(float* v, int lane) {
 // statistics; the register butterfly (colsum32 twice: 62 SHFL + 124 FSEL + 62 FADD) was ~46 % of all
 // instructions of the epilogue-bound 1x1 layers (profiles/r1_end_ncu_full_conv_tc_1x1_64_256.txt).
 constexpr int TR_BYTES = 32 * 64;
-__device__ __forceinline__ void colstats32(const float* v, uint8_t* tr, int lane, float& s_out, float& q_out) {
-  uint32_t pk[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+// lane's row (32 bf16 = 4 x 16 B) -> the warp's transpose scratch
+__device__ __forceinline__ void tr_write_row(uint8_t* tr, int lane, const uint32_t* pk) {
   const int sw = (lane >> 1) & 3;
 #pragma unroll
   for (int c = 0; c < 4; ++c)
     *reinterpret_cast<uint4*>(tr + lane * 64 + ((c ^ sw) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
-  __syncwarp();
+}
+// column sums / sums of squares of the block in the scratch: lane j walks column j
+__device__ __forceinline__ void tr_colstats(const uint8_t* tr, int lane, float& s_out, float& q_out) {
   const int cw = lane >> 3, wofs = ((lane & 7) >> 1) * 4;
   const uint32_t sel = (lane & 1) ? 0x3244u : 0x1044u;      // bf16 half of the word -> fp32 bits
-  float s = 0.f, q = 0.f;
+  // four independent accumulator pairs: one serial FADD / FFMA chain over the 32 rows was ~130 cycles of pure latency per
+  // block, exposed with two epilogue warps per scheduler
+  float s4[4] = {0.f, 0.f, 0.f, 0.f}, q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int r = 0; r < 32; ++r) {
     const uint32_t w = *reinterpret_cast<const uint32_t*>(tr + r * 64 + ((cw ^ ((r >> 1) & 3)) << 4) + wofs);
     const float f = __uint_as_float(__byte_perm(w, 0u, sel));
-    s += f;
-    q = fmaf(f, f, q);
+    s4[r & 3] += f;
+    q4[r & 3] = fmaf(f, f, q4[r & 3]);
   }
+  s_out = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+  q_out = (q4[0] + q4[1]) + (q4[2] + q4[3]);
+}
+// The block in the scratch -> global memory, FOUR lanes per pixel row: one store instruction covers 8 rows x 64
+// contiguous bytes (16 whole sectors).  The thread-per-row form (32 rows x 16 B per instruction) cost 32 LSU wavefronts
+// per store and sent every 32-byte sector to L2 twice, half filled (ncu on the 1x1 64 -> 256 layer: LSU data pipe 67 %
+// busy, 269 MB from L1 to the crossbar for 134 MB of output): that, not the tensor pipe or DRAM, bound the wide layers.
+// pix: the calling lane's own output pixel (lane = row of the block); the rows' pixels are fetched by shuffle.
+__device__ __forceinline__ void tr_store_rows(const uint8_t* tr, int lane, long long pix, bf16* y, int ldy, int ch0) {
+  const int cc = lane & 3;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = (lane >> 2) + 8 * i;
+    const long long pr = __shfl_sync(0xffffffffu, pix, r);
+    const uint4 d = *reinterpret_cast<const uint4*>(tr + r * 64 + ((cc ^ ((r >> 1) & 3)) << 4));
+    *reinterpret_cast<uint4*>(y + pr * ldy + ch0 + cc * 8) = d;
+  }
+}
+// One 32 x 32 block of the epilogue: BatchNorm statistics of the bf16-rounded pre-activation values (optional),
+// activation, coalesced store.  All lanes of the warp; two or three __syncwarp per block.
+__device__ __forceinline__ void epilogue_block32(const float* v, uint8_t* tr, int lane, bool stats, int act, float& s_out,
+                                                 float& q_out, long long pix, bf16* y, int ldy, int ch0) {
+  uint32_t pk[16];
+  if (stats || act == HN_ACT_NONE) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+    tr_write_row(tr, lane, pk);
+    __syncwarp();
+    if (stats) tr_colstats(tr, lane, s_out, q_out);
+    if (stats && act != HN_ACT_NONE) __syncwarp();
+  }
+  if (act != HN_ACT_NONE) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(apply_act(v[2 * j], act), apply_act(v[2 * j + 1], act));
+    tr_write_row(tr, lane, pk);
+    __syncwarp();
+  }
+  tr_store_rows(tr, lane, pix, y, ldy, ch0);
   __syncwarp();
-  s_out = s;
-  q_out = q;
 }
 
-template <int BN, int BKC>
-__global__ void __launch_bounds__(NTHREADS_TC, 1)
+// TEAMS = epilogue warps per TMEM lane quadrant (the teams take alternate 32-column chunks of a tile).  Layers with a
+// short K loop (1x1 convs, C <= 256) are bound by the epilogue's latency chain (tcgen05.ld -> bias -> statistics through
+// shared memory -> stores; ncu: 30 % issue utilisation with two warps per scheduler), not by issue slots or DRAM: they
+// run with four teams (16 epilogue warps, a shallower operand pipeline that they do not need); long-K layers keep two
+// teams and the deepest pipeline that fits.
+template <int BN, int TEAMS>
+struct TcCfg {
+  static constexpr int NTHR = 64 + 128 * TEAMS;
+  static constexpr int TR_TOTAL = TEAMS * 4 * TR_BYTES;
+  static constexpr int MAXC = (BN / 32 + TEAMS - 1) / TEAMS;       // chunks per epilogue warp and tile
+};
+template <int BN, int BKC, int TEAMS>
+__host__ __device__ constexpr int tc_stages() {
+  constexpr int stage = BM * BKC * 2 + BN * BKC * 2;
+  constexpr int budget = 208 * 1024 - TcCfg<BN, TEAMS>::TR_TOTAL;
+  return budget / stage > 8 ? 8 : budget / stage;
+}
+
+template <int BN, int BKC, int TEAMS>
+__global__ void __launch_bounds__((64 + 128 * TEAMS), 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapB, const TcParams p) {
   constexpr int A_BYTES = BM * BKC * 2;
   constexpr int B_BYTES = BN * BKC * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr int STAGES = (192 * 1024 / STAGE_BYTES) > 8 ? 8 : (192 * 1024 / STAGE_BYTES);
+  constexpr int STAGES = tc_stages<BN, BKC, TEAMS>();
+  constexpr int NTHR = TcCfg<BN, TEAMS>::NTHR;
+  constexpr int MAXC = TcCfg<BN, TEAMS>::MAXC;
   constexpr int ACC_STRIDE = BN <= 64 ? 64 : (BN <= 128 ? 128 : 256);
   constexpr int TMEM_COLS = 2 * ACC_STRIDE;
   constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
@@ -195,9 +253,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   // BatchNorm sum / sum-of-squares are accumulated per CTA here and flushed with ONE global atomic per
   // channel per CTA at the end (per-tile global atomics serialise on the same few addresses in L2)
   __shared__ float s_stat[2][STAT_MAX];
-  __shared__ __align__(16) uint8_t s_tr[8][TR_BYTES];       // per epilogue warp: transpose scratch of colstats32
+  uint8_t* s_tr = smem + STAGES * STAGE_BYTES;               // per epilogue warp: transpose scratch of colstats32
   if (p.ssum) {
-    for (int i = threadIdx.x; i < 2 * STAT_MAX; i += NTHREADS_TC) (&s_stat[0][0])[i] = 0.f;
+    for (int i = threadIdx.x; i < 2 * STAT_MAX; i += NTHR) (&s_stat[0][0])[i] = 0.f;
   }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -206,7 +264,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull0 + 8 * a, 1); mbar_init(tempty0 + 8 * a, 4 * TEAMS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -281,6 +339,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     // ---- epilogue warps: TMEM lanes [32*(warp%4), +32) = tile rows ----------------------
     const int lane_base = (warp & 3) * 32;
     const int row = lane_base + lane;
+    const int team = (warp - 2) >> 2;
+    uint8_t* tr = s_tr + (warp - 2) * TR_BYTES;
+    // BatchNorm statistics: with one n-tile every tile of this CTA shows a warp the SAME channels, so lane j keeps the
+    // running sums of its column (chunk ci, column j) in registers and touches shared memory once, after the last tile
+    const bool reg_stats = p.ssum != nullptr && p.n_tiles == 1;
+    float acc_s[MAXC], acc_q[MAXC];
+#pragma unroll
+    for (int ci = 0; ci < MAXC; ++ci) acc_s[ci] = acc_q[ci] = 0.f;
     int lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int nt = tile % p.n_tiles, mt = tile / p.n_tiles;
@@ -292,9 +358,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       mbar_wait(tfull0 + 8 * acc, acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)lane_base << 16) + acc * ACC_STRIDE;
-#pragma unroll 1
-      // the two warps of a lane quadrant take alternate 32-column chunks
-      for (int c = (warp - 2) >> 2; c < BN / 32; c += 2) {
+      // the teams of a lane quadrant take alternate 32-column chunks
+#pragma unroll
+      for (int ci = 0; ci < MAXC; ++ci) {
+        const int c = team + ci * TEAMS;
+        if (c >= BN / 32) break;
         uint32_t r[32];
         tmem_ld32(t_row + c * 32, r);
         const int n = nt * BN + c * 32;        // first GEMM column of this chunk
@@ -321,19 +389,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __ldg(p.bias + ch0 + j);
         }
+        float s = 0.f, q = 0.f;
+        epilogue_block32(v, tr, lane, p.ssum != nullptr, p.act, s, q, pix, p.y, p.ldy, ch0);
         if (p.ssum) {
-          float s, q;
-          colstats32(v, s_tr[warp - 2], lane, s, q);
-          atomicAdd(&s_stat[0][ch0 + lane], s);
-          atomicAdd(&s_stat[1][ch0 + lane], q);
-        }
-        bf16* dst = p.y + pix * p.ldy + ch0;
-#pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-          float o[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) o[e] = apply_act(v[j + e], p.act);
-          store8(dst + j, o);
+          if (reg_stats && !p.pshuf) {
+            acc_s[ci] += s;
+            acc_q[ci] += q;
+          } else {
+            atomicAdd(&s_stat[0][ch0 + lane], s);
+            atomicAdd(&s_stat[1][ch0 + lane], q);
+          }
         }
       }
       tc_fence_before();
@@ -341,9 +406,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
     }
     if (p.ssum) {
-      asm volatile("bar.sync 1, 256;" ::: "memory");            // the eight epilogue warps only
+      if (reg_stats && !p.pshuf) {
+#pragma unroll
+        for (int ci = 0; ci < MAXC; ++ci) {
+          const int c = team + ci * TEAMS;
+          if (c < BN / 32) {
+            atomicAdd(&s_stat[0][c * 32 + lane], acc_s[ci]);
+            atomicAdd(&s_stat[1][c * 32 + lane], acc_q[ci]);
+          }
+        }
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(128 * TEAMS) : "memory");            // the epilogue warps only
       const int nstat = p.pshuf ? p.pshuf : p.Ntot;
-      for (int i = threadIdx.x - 64; i < nstat; i += 256) {
+      for (int i = threadIdx.x - 64; i < nstat; i += 128 * TEAMS) {
         const float a = s_stat[0][i], b = s_stat[1][i];
         if (a != 0.f || b != 0.f) { atomicAdd(p.ssum + i, a); atomicAdd(p.ssq + i, b); }
       }
@@ -505,19 +580,11 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(p.bias + ch0 + j) : 0.f);
+        float s = 0.f, q = 0.f;
+        epilogue_block32(v, s_tr[warp - 2], lane, p.ssum != nullptr, p.act, s, q, pix, p.y, p.ldy, ch0);
         if (p.ssum) {
-          float s, q;
-          colstats32(v, s_tr[warp - 2], lane, s, q);
           atomicAdd(&s_stat[0][ch0 + lane], s);
           atomicAdd(&s_stat[1][ch0 + lane], q);
-        }
-        bf16* dst = p.y + pix * p.ldy + ch0;
-#pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-          float o[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) o[e] = apply_act(v[j + e], p.act);
-          store8(dst + j, o);
         }
       }
       tc_fence_before();
@@ -620,22 +687,37 @@ int make_map_w(CUtensorMap* m, const void* ptr, int Npad, int Kpad, int BN, int 
   return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
-template <int BN, int BKC>
-int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& bm, const TcParams& p, cudaStream_t st) {
+template <int BN, int BKC, int TEAMS>
+int launch_tc_t(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& bm, const TcParams& p, cudaStream_t st) {
   constexpr int STAGE_BYTES = BM * BKC * 2 + BN * BKC * 2;
-  constexpr int STAGES = (192 * 1024 / STAGE_BYTES) > 8 ? 8 : (192 * 1024 / STAGE_BYTES);
-  constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
+  constexpr int STAGES = tc_stages<BN, BKC, TEAMS>();
+  constexpr int SMEM = STAGES * STAGE_BYTES + TcCfg<BN, TEAMS>::TR_TOTAL + 1024;
+  static_assert(STAGES >= 2, "conv_tc: operand pipeline too shallow");
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<BN, BKC, TEAMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) HN_FAIL(HN_ECUDA, "conv_tc: smem attribute: %s", cudaGetErrorString(e));
     configured = true;
   }
   int tiles = p.m_tiles * p.n_tiles;
   int grid = tiles < 148 ? tiles : 148;
-  conv_tc_kernel<BN, BKC><<<grid, NTHREADS_TC, SMEM, st>>>(a1, a2, bm, p);
+  conv_tc_kernel<BN, BKC, TEAMS><<<grid, TcCfg<BN, TEAMS>::NTHR, SMEM, st>>>(a1, a2, bm, p);
   HN_CHECK_LAUNCH("conv_tc_kernel");
   return HN_OK;
+}
+template <int BN, int BKC>
+int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& bm, const TcParams& p, cudaStream_t st) {
+  // short K loop and a wide tile: the epilogue binds, four teams (see conv_tc_kernel)
+  const int kiters = p.KH * p.KW * (p.kiters_per_tap1 + p.kiters_per_tap2);
+  // measured on the 1x1 64 -> 256 layer (B = 16, 128 x 128), us with / without BatchNorm statistics: two teams 59.0 / 44.7,
+  // three 71.2 / 47.3, four (96 registers, spills) 66.8 / 40.8 -- more epilogue warps only pay without the statistics, and
+  // every wide layer of these nets feeds a BatchNorm: two teams everywhere unless built with -DHN_TC_WIDE_TEAMS=4
+#ifndef HN_TC_WIDE_TEAMS
+#define HN_TC_WIDE_TEAMS 2
+#endif
+  if (HN_TC_WIDE_TEAMS > 2 && BN >= 128 && BKC == 64 && kiters <= 4)
+    return launch_tc_t<BN, BKC, (BN >= 128 && BKC == 64) ? HN_TC_WIDE_TEAMS : 2>(a1, a2, bm, p, st);
+  return launch_tc_t<BN, BKC, 2>(a1, a2, bm, p, st);
 }
 
 // ---- halo variant host side ------------------------------------------------------------------------
