@@ -493,8 +493,12 @@ def run_ours(args, workload, B, rank, world, local, dev, steps, warmup, with_cpu
         _lib.set_profiler(prof)
         psteps = 2
         arena.exchange = False                  # rank-0-only pass: no collectives (the other ranks are at the barrier)
+        # per-kernel durations are taken one kernel at a time: the weight gradients stay on the main stream here (in the
+        # timed step they run on a side stream beside the input gradient, which would stretch both event intervals)
+        overlap, ops.WGRAD_OVERLAP = ops.WGRAD_OVERLAP, False
         for _ in range(psteps):
             step(x, y)
+        ops.WGRAD_OVERLAP = overlap
         arena.exchange = True
         _lib.set_profiler(None)
         agg = prof.table()

@@ -152,15 +152,29 @@ __device__ __forceinline__ float colsum32(float* v, int lane) {
 // statistics; the register butterfly (colsum32 twice: 62 SHFL + 124 FSEL + 62 FADD) was ~46 % of all
 // instructions of the epilogue-bound 1x1 layers (profiles/r1_end_ncu_full_conv_tc_1x1_64_256.txt).
 constexpr int TR_BYTES = 32 * 64;
+// The scratch is addressed through the shared window (32-bit address, ld/st.shared): it may sit in the dynamic part of
+// shared memory, where a C++ pointer makes the compiler fall back to generic LD / ST.
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_v4(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
 // lane's row (32 bf16 = 4 x 16 B) -> the warp's transpose scratch
-__device__ __forceinline__ void tr_write_row(uint8_t* tr, int lane, const uint32_t* pk) {
+__device__ __forceinline__ void tr_write_row(uint32_t tr, int lane, const uint32_t* pk) {
   const int sw = (lane >> 1) & 3;
 #pragma unroll
-  for (int c = 0; c < 4; ++c)
-    *reinterpret_cast<uint4*>(tr + lane * 64 + ((c ^ sw) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+  for (int c = 0; c < 4; ++c) sts_v4(tr + lane * 64 + ((c ^ sw) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
 }
 // column sums / sums of squares of the block in the scratch: lane j walks column j
-__device__ __forceinline__ void tr_colstats(const uint8_t* tr, int lane, float& s_out, float& q_out) {
+__device__ __forceinline__ void tr_colstats(uint32_t tr, int lane, float& s_out, float& q_out) {
   const int cw = lane >> 3, wofs = ((lane & 7) >> 1) * 4;
   const uint32_t sel = (lane & 1) ? 0x3244u : 0x1044u;      // bf16 half of the word -> fp32 bits
   // four independent accumulator pairs: one serial FADD / FFMA chain over the 32 rows was ~130 cycles of pure latency per
@@ -168,7 +182,7 @@ __device__ __forceinline__ void tr_colstats(const uint8_t* tr, int lane, float& 
   float s4[4] = {0.f, 0.f, 0.f, 0.f}, q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
   for (int r = 0; r < 32; ++r) {
-    const uint32_t w = *reinterpret_cast<const uint32_t*>(tr + r * 64 + ((cw ^ ((r >> 1) & 3)) << 4) + wofs);
+    const uint32_t w = lds_u32(tr + r * 64 + ((cw ^ ((r >> 1) & 3)) << 4) + wofs);
     const float f = __uint_as_float(__byte_perm(w, 0u, sel));
     s4[r & 3] += f;
     q4[r & 3] = fmaf(f, f, q4[r & 3]);
@@ -181,19 +195,19 @@ __device__ __forceinline__ void tr_colstats(const uint8_t* tr, int lane, float& 
 // per store and sent every 32-byte sector to L2 twice, half filled (ncu on the 1x1 64 -> 256 layer: LSU data pipe 67 %
 // busy, 269 MB from L1 to the crossbar for 134 MB of output): that, not the tensor pipe or DRAM, bound the wide layers.
 // pix: the calling lane's own output pixel (lane = row of the block); the rows' pixels are fetched by shuffle.
-__device__ __forceinline__ void tr_store_rows(const uint8_t* tr, int lane, long long pix, bf16* y, int ldy, int ch0) {
+__device__ __forceinline__ void tr_store_rows(uint32_t tr, int lane, long long pix, bf16* y, int ldy, int ch0) {
   const int cc = lane & 3;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int r = (lane >> 2) + 8 * i;
     const long long pr = __shfl_sync(0xffffffffu, pix, r);
-    const uint4 d = *reinterpret_cast<const uint4*>(tr + r * 64 + ((cc ^ ((r >> 1) & 3)) << 4));
+    const uint4 d = lds_v4(tr + r * 64 + ((cc ^ ((r >> 1) & 3)) << 4));
     *reinterpret_cast<uint4*>(y + pr * ldy + ch0 + cc * 8) = d;
   }
 }
 // One 32 x 32 block of the epilogue: BatchNorm statistics of the bf16-rounded pre-activation values (optional),
 // activation, coalesced store.  All lanes of the warp; two or three __syncwarp per block.
-__device__ __forceinline__ void epilogue_block32(const float* v, uint8_t* tr, int lane, bool stats, int act, float& s_out,
+__device__ __forceinline__ void epilogue_block32(const float* v, uint32_t tr, int lane, bool stats, int act, float& s_out,
                                                  float& q_out, long long pix, bf16* y, int ldy, int ch0) {
   uint32_t pk[16];
   if (stats || act == HN_ACT_NONE) {
@@ -340,7 +354,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     const int lane_base = (warp & 3) * 32;
     const int row = lane_base + lane;
     const int team = (warp - 2) >> 2;
-    uint8_t* tr = s_tr + (warp - 2) * TR_BYTES;
+    const uint32_t tr = smem_u32(s_tr) + (warp - 2) * TR_BYTES;
     // BatchNorm statistics: with one n-tile every tile of this CTA shows a warp the SAME channels, so lane j keeps the
     // running sums of its column (chunk ci, column j) in registers and touches shared memory once, after the last tile
     const bool reg_stats = p.ssum != nullptr && p.n_tiles == 1;
@@ -581,7 +595,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + (p.bias ? __ldg(p.bias + ch0 + j) : 0.f);
         float s = 0.f, q = 0.f;
-        epilogue_block32(v, s_tr[warp - 2], lane, p.ssum != nullptr, p.act, s, q, pix, p.y, p.ldy, ch0);
+        epilogue_block32(v, smem_u32(s_tr[warp - 2]), lane, p.ssum != nullptr, p.act, s, q, pix, p.y, p.ldy, ch0);
         if (p.ssum) {
           atomicAdd(&s_stat[0][ch0 + lane], s);
           atomicAdd(&s_stat[1][ch0 + lane], q);
@@ -709,9 +723,9 @@ template <int BN, int BKC>
 int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& bm, const TcParams& p, cudaStream_t st) {
   // short K loop and a wide tile: the epilogue binds, four teams (see conv_tc_kernel)
   const int kiters = p.KH * p.KW * (p.kiters_per_tap1 + p.kiters_per_tap2);
-  // measured on the 1x1 64 -> 256 layer (B = 16, 128 x 128), us with / without BatchNorm statistics: two teams 59.0 / 44.7,
-  // three 71.2 / 47.3, four (96 registers, spills) 66.8 / 40.8 -- more epilogue warps only pay without the statistics, and
-  // every wide layer of these nets feeds a BatchNorm: two teams everywhere unless built with -DHN_TC_WIDE_TEAMS=4
+  // measured on the 1x1 64 -> 256 layer (B = 16, 128 x 128) with BatchNorm statistics: two teams 49.3 us, three 48.4, four
+  // (96 registers, spills) 46.8; 1x1 128 -> 512: 32.2 / 31.4 / 30.1.  Not worth a second kernel shape: two teams
+  // everywhere unless built with -DHN_TC_WIDE_TEAMS=3|4
 #ifndef HN_TC_WIDE_TEAMS
 #define HN_TC_WIDE_TEAMS 2
 #endif
