@@ -559,6 +559,42 @@ def _side_stream(dev):
     return st
 
 
+# A weight gradient that a kernel reduces straight into the gradient arena (the sink) has no consumer before the gradient
+# exchange / the optimizer, so the side stream need not rejoin after every layer: it runs on beside the backward kernels
+# of the layers that follow (most of them launch fewer CTAs than there are SMs) and rejoins ONCE, in a callback the
+# autograd engine runs at the end of the backward pass.  The tensors a deferred kernel reads are kept alive until then;
+# GradArena makes its all-reduce stream wait for the side stream as well (deferred_side_stream).
+WGRAD_DEFER = True
+_deferred = {"refs": [], "side": None, "main": None}
+
+
+def _join_deferred():
+    st = _deferred
+    if st["side"] is not None:
+        st["main"].wait_stream(st["side"])
+    st["refs"].clear()
+    st["side"] = st["main"] = None
+
+
+def _defer_join(main, side, tensors):
+    st = _deferred
+    if st["side"] is None:
+        try:
+            torch.autograd.Variable._execution_engine.queue_callback(_join_deferred)
+        except RuntimeError:          # not inside a backward pass
+            return False
+        st["side"], st["main"] = side, main
+    elif st["side"] is not side or st["main"] != main:
+        return False
+    st["refs"].append(tensors)
+    return True
+
+
+def deferred_side_stream():
+    """The side stream with weight-gradient kernels still to be joined (None when there is none)."""
+    return _deferred["side"]
+
+
 def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
     """dz: gradient at the conv output (NHWC, padded channels zero). Returns dx1, dx2, dW."""
     if not (WGRAD_OVERLAP and need_dx and need_dw):
@@ -620,7 +656,8 @@ def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side):
             dx1 = full[..., :C1] if C2 else full
             dx2 = full[..., C1:] if C2 else None
     if side is not None:
-        main.wait_stream(side)
+        if not (sunk is not None and WGRAD_DEFER and _defer_join(main, side, (dz, x1, x2))):
+            main.wait_stream(side)
     if sunk is not None:
         _sink_done(weight.data_ptr())
         dw = None

@@ -150,7 +150,11 @@ class GradArena:
     def _launch(self, b):
         lo, hi = self.bucket_range[b]
         if self.comm is not None:
+            from . import ops
             self.comm.wait_stream(torch.cuda.current_stream())
+            side = ops.deferred_side_stream()          # weight gradients still running beside the backward pass
+            if side is not None:
+                self.comm.wait_stream(side)
             with torch.cuda.stream(self.comm):
                 self.works.append(dist.all_reduce(self.arena[lo:hi], op=dist.ReduceOp.SUM, group=self.group,
                                                   async_op=True))
