@@ -83,17 +83,23 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
     const int tw = tile % p.tiles_w, th = (tile / p.tiles_w) % p.tiles_h, b = tile / (p.tiles_w * p.tiles_h);
     const int h0 = th * TH, w0 = tw * TW;
     uint8_t* dstb = sH + buf * halo_bytes;
-    for (int id = tid; id < halo_chunks; id += SC_THREADS) {
-      const int c8 = id & cgm;
-      const int pc = id >> p.lgCG;
-      const int r = pc / p.WR, c = pc - r * p.WR;
-      const int ih = h0 - p.pad + r, iw = w0 - p.pad + c;
-      const bool ok = (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
-      const int sh_ = ok ? ih : 0, sw_ = ok ? iw : 0;
-      const long long pix = p.ups ? ((long long)b * (p.H >> 1) + (sh_ >> 1)) * (p.W >> 1) + (sw_ >> 1)
-                                  : ((long long)b * p.H + sh_) * p.W + sw_;
-      const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
-      cp_async16(smem_u32(dstb + ((pc << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
+    // one warp per halo row, lanes over the row's 16-byte chunks (no per-chunk division; the 64-bit row base once per row)
+    const uint32_t dsta = smem_u32(dstb);
+    for (int r = warp; r < p.HR; r += SC_THREADS / 32) {
+      const int ih = h0 - p.pad + r;
+      const bool rok = (unsigned)ih < (unsigned)p.H;
+      const int srow = rok ? ih : 0;
+      const long long rowpix = p.ups ? ((long long)b * (p.H >> 1) + (srow >> 1)) * (p.W >> 1) : ((long long)b * p.H + srow) * p.W;
+      const uint32_t rowaddr = dsta + (uint32_t)(((r * p.WR) << p.lgCG) * 16);
+      for (int idx = lane; idx < (p.WR << p.lgCG); idx += 32) {
+        const int c = idx >> p.lgCG, c8 = idx & cgm;
+        const int iw = w0 - p.pad + c;
+        const bool ok = rok && (unsigned)iw < (unsigned)p.W;
+        const int sw_ = ok ? iw : 0;
+        const long long pix = rowpix + (p.ups ? (sw_ >> 1) : sw_);
+        const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
+        cp_async16(rowaddr + (uint32_t)(((c << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
+      }
     }
   };
   // two halo buffers: the next tile streams in while this one is computed (keeps loads in flight)

@@ -31,7 +31,7 @@ struct WsP {
 };
 
 template <int MTN, int CPW>   // 16-row blocks of Cout, column chunks per warp
-__global__ void __launch_bounds__(WS_THREADS) wgrad_sc_kernel(const WsP p) {
+__global__ void __launch_bounds__(WS_THREADS, 2) wgrad_sc_kernel(const WsP p) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int s_tap[9];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -66,54 +66,81 @@ __global__ void __launch_bounds__(WS_THREADS) wgrad_sc_kernel(const WsP p) {
     c_dc[j] = s_tap[tap] & 0xFFFF;
   }
 
+  // Shared-memory byte offsets of this lane's ldmatrix rows, without the tile-row term: the swizzle key of a halo pixel
+  // depends only on its column, the key of a dz pixel only on the low bits of its index, so everything but
+  // (row * pitch) is a per-warp constant.  Computed per k-step (with run-time shifts) this address arithmetic was 17
+  // instructions per HMMA: 25 % IMAD, 12 % SHF, 12 % LOP3 against 6 % HMMA in the ncu instruction mix of the C = 32 layers.
+  const uint32_t sH_addr = smem_u32(sH), sD_addr = smem_u32(sD);
+  // (the key uses column bits below 4 only, so the second 16-pixel half of a row is a constant 16 pixels further on)
+  uint32_t b_off[CPW], a_off[MTN];
+#pragma unroll
+  for (int j = 0; j < CPW; ++j) {
+    const int cc0 = (lane & 15) + c_dc[j];
+    b_off[j] = (uint32_t)((((c_dr[j] * p.WR + cc0) << p.lgCG) + (c_c8[j] ^ ((cc0 >> p.sh) & cgm))) * 16);
+  }
+  if (NC == 1) {
+    a_off[0] = (uint32_t)((lane & 15) * 16);
+  } else {
+    const int ql = (lane & 7) + ((lane >> 4) << 3);       // pixel of this lane's row inside the 16-pixel k-step
+#pragma unroll
+    for (int i = 0; i < MTN; ++i) {
+      const int nc = i * 2 + ((lane >> 3) & 1);
+      a_off[i] = (uint32_t)(((ql << p.lgNC) + (nc ^ ((ql >> p.shn) & ncm))) * 16);
+    }
+  }
+
   for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
     const int tw = tile % p.tiles_w, th = (tile / p.tiles_w) % p.tiles_h, b = tile / (p.tiles_w * p.tiles_h);
     const int h0 = th * TH, w0 = tw * TW;
     __syncthreads();                                       // previous tile fully consumed
-    for (int id = tid; id < halo_chunks; id += WS_THREADS) {
-      const int c8 = id & cgm;
-      const int pc = id >> p.lgCG;
-      const int r = pc / p.WR, c = pc - r * p.WR;
-      const int ih = h0 - p.pad + r, iw = w0 - p.pad + c;
-      const bool ok = (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
-      const int sh_ = ok ? ih : 0, sw_ = ok ? iw : 0;
-      const long long pix = p.ups ? ((long long)b * (p.H >> 1) + (sh_ >> 1)) * (p.W >> 1) + (sw_ >> 1)
-                                  : ((long long)b * p.H + sh_) * p.W + sw_;
-      const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
-      cp_async16(smem_u32(sH + ((pc << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
+    // one warp per halo / tile row, lanes over the row's 16-byte chunks: no per-chunk division, the 64-bit row base once per
+    // row (the flat-index form spent ~80 instructions per chunk: half of the kernel's instructions on the C = 32 layers)
+    for (int r = warp; r < p.HR; r += WS_THREADS / 32) {
+      const int ih = h0 - p.pad + r;
+      const bool rok = (unsigned)ih < (unsigned)p.H;
+      const int srow = rok ? ih : 0;
+      const long long rowpix = p.ups ? ((long long)b * (p.H >> 1) + (srow >> 1)) * (p.W >> 1) : ((long long)b * p.H + srow) * p.W;
+      const uint32_t rowaddr = sH_addr + (uint32_t)(((r * p.WR) << p.lgCG) * 16);
+      for (int idx = lane; idx < (p.WR << p.lgCG); idx += 32) {
+        const int c = idx >> p.lgCG, c8 = idx & cgm;
+        const int iw = w0 - p.pad + c;
+        const bool ok = rok && (unsigned)iw < (unsigned)p.W;
+        const int sw_ = ok ? iw : 0;
+        const long long pix = rowpix + (p.ups ? (sw_ >> 1) : sw_);
+        const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
+        cp_async16(rowaddr + (uint32_t)(((c << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
+      }
     }
-    for (int id = tid; id < TH * TW * NC; id += WS_THREADS) {
-      const int nc = id & ncm;
-      const int q = id >> p.lgNC;                           // pixel inside the tile: row q>>5, col q&31
-      const long long pix = ((long long)b * p.H + h0 + (q >> 5)) * p.W + w0 + (q & 31);
-      cp_async16(smem_u32(sD + ((q << p.lgNC) + (nc ^ ((q >> p.shn) & ncm))) * 16), p.dz + pix * p.lddz + nc * 8, true);
+    for (int r = warp; r < TH; r += WS_THREADS / 32) {
+      const long long rowpix = ((long long)b * p.H + h0 + r) * p.W + w0;
+      for (int idx = lane; idx < (TW << p.lgNC); idx += 32) {
+        const int cpx = idx >> p.lgNC, nc = idx & ncm;
+        const int q = r * TW + cpx;
+        cp_async16(sD_addr + (uint32_t)(((q << p.lgNC) + (nc ^ ((q >> p.shn) & ncm))) * 16), p.dz + (rowpix + cpx) * p.lddz + nc * 8, true);
+      }
     }
     cp_async_commit();
     cp_async_wait<0>();
     __syncthreads();
 
     for (int ks = wk; ks < TH * 2; ks += p.ksplit) {       // 16 pixels of one tile row per k-step
-      const int r = ks >> 1, c0 = (ks & 1) * 16;
+      const int r = ks >> 1, hsel = ks & 1;
       // A fragments: dz^T  (rows = output channels, k = pixels)
       uint32_t a[MTN][4];
+      const uint32_t arow = sD_addr + (uint32_t)(((r * 32 + hsel * 16) << p.lgNC) * 16);
       if (NC == 1) {
-        const int q = r * 32 + c0 + (lane & 15);
-        ldsm_x2_t(a[0][0], a[0][2], smem_u32(sD + q * 16));
+        ldsm_x2_t(a[0][0], a[0][2], arow + a_off[0]);
         a[0][1] = a[0][3] = 0u;
       } else {
-        const int q = r * 32 + c0 + (lane & 7) + ((lane >> 4) << 3);
 #pragma unroll
-        for (int i = 0; i < MTN; ++i) {
-          const int nc = i * 2 + ((lane >> 3) & 1);
-          ldsm_x4_t(a[i][0], a[i][1], a[i][2], a[i][3], smem_u32(sD + ((q << p.lgNC) + (nc ^ ((q >> p.shn) & ncm))) * 16));
-        }
+        for (int i = 0; i < MTN; ++i) ldsm_x4_t(a[i][0], a[i][1], a[i][2], a[i][3], arow + a_off[i]);
       }
+      const uint32_t brow = sH_addr + (uint32_t)(((r * p.WR + hsel * 16) << p.lgCG) * 16);
 #pragma unroll
       for (int j = 0; j < CPW; ++j) {
         if (!c_ok[j]) continue;                            // warp-uniform
-        const int rr = r + c_dr[j], cc = c0 + (lane & 15) + c_dc[j];
         uint32_t b0, b1;
-        ldsm_x2_t(b0, b1, smem_u32(sH + (((rr * p.WR + cc) << p.lgCG) + (c_c8[j] ^ ((cc >> p.sh) & cgm))) * 16));
+        ldsm_x2_t(b0, b1, brow + b_off[j]);
 #pragma unroll
         for (int i = 0; i < MTN; ++i) mma_16816(acc[i][j], a[i], b0, b1);
       }
