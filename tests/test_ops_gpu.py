@@ -57,6 +57,9 @@ CONV_CASES = [
     (256, 512, 1, 2, 0, 1, 16, "none", False),   # downsample 1x1 stride 2
     (192, 64, 3, 1, 1, 1, 16, "none", True),     # Decoder_32K conv5
     (32, 1, 1, 1, 0, 1, 16, "sigmoid", True),    # UNet head 1x1
+    (64, 64, 3, 1, 1, 1, 64, "none", False),     # UNet level 2 at W >= 64: the row-halo form of the tcgen05 weight gradient
+    (128, 96, 3, 1, 1, 1, 64, "none", True),     # two 64-channel boxes per side, Cout not a multiple of 64
+    (64, 128, 3, 1, 2, 2, 128, "none", False),   # halo with dilation 2, two 64-pixel steps per image row
 ]
 
 

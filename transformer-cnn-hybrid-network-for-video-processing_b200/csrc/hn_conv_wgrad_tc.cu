@@ -34,6 +34,11 @@ struct WgTc {
   float* dw;
   float* ws;                                // optional partial-sum workspace [splits][taps][Cout][Ctot] (two-stage reduce)
   int Ctot;
+  // halo mode (3x3, stride 1, OW % 64 == 0, <= 128 channels per side): a work item owns ONE filter row (3 taps); per
+  // pixel step it fetches a single x box of 64 + 2*dil pixels of the image row and the three kw taps are the same box
+  // read through descriptors whose start is shifted by kw*dil pixel rows (128 B each) -- x crosses L2 three times per
+  // layer instead of nine (the tap-shifted boxes made the C = 64 / 128 layers L2-bound: 208 / 395 TFLOP/s)
+  int halo, hb;                             // flag; bytes of one halo box, rounded up to 1 KB
 };
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -144,7 +149,8 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
   const int aboxes = min(mtiles * 2, (p.Cout - n_off + 63) / 64);
   // this item's taps [tap0, tap0 + ntap): each (tap, m-tile) owns ncols TMEM columns, dz is fetched once
   const int tap0 = tg * p.tpj, ntap = min(p.tpj, taps - tap0);
-  const int stage_bytes = (aboxes + ntap * nboxes) * BOX_BYTES;
+  const int stage_bytes = p.halo ? aboxes * BOX_BYTES + nboxes * p.hb : (aboxes + ntap * nboxes) * BOX_BYTES;
+  const int tx_bytes = p.halo ? aboxes * BOX_BYTES + nboxes * (PK + 2 * p.dil) * 128 : stage_bytes;
   const int nstages = p.stages;
   const int t0 = split * p.tiles_per_split, t1 = min(p.ptiles, t0 + p.tiles_per_split);
 
@@ -172,8 +178,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
         const int w0 = tw * p.BW, h0 = th * p.BH, b0 = tb * p.BB;
         mbar_wait(empty0 + 8 * stage, phase ^ 1);
         const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-        mbar_arrive_expect_tx(full0 + 8 * stage, stage_bytes);
+        mbar_arrive_expect_tx(full0 + 8 * stage, tx_bytes);
         for (int i = 0; i < aboxes; ++i) tma_load_4d(sa + i * BOX_BYTES, &mapDZ, full0 + 8 * stage, n_off + i * 64, w0, h0, b0);
+        if (p.halo) {
+          const int kh = tap0 / p.KW;
+          for (int i = 0; i < nboxes; ++i)
+            tma_load_4d(sa + aboxes * BOX_BYTES + i * p.hb, mx, full0 + 8 * stage, c_off + i * 64, w0 - p.pad, h0 + kh * p.dil - p.pad, b0);
+        } else
         for (int ti = 0; ti < ntap; ++ti) {
           const int kh = (tap0 + ti) / p.KW, kw = (tap0 + ti) - kh * p.KW;
           const int xw = w0 * p.es + kw * p.dil - p.pad, xh = h0 * p.es + kh * p.dil - p.pad;
@@ -190,20 +201,30 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapDZ, const __grid_constant
     // M = 128, N = ncols, A and B both MN-major (bits 15, 16), bf16 in, fp32 accumulate
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(ncols >> 3) << 17) | (8u << 24);
     const uint32_t smem_base = smem_u32(smem);
+    // Descriptors: everything but the 14-bit start-address field is fixed for the whole item, so per MMA the issuing
+    // thread only adds an offset (>> 4) to a template.  Built from scratch per MMA (two make_mn_desc, run-time selects)
+    // the single issuing warp needed ~1200 clocks per pixel step against ~580 of tensor / shared-memory time: the
+    // kernel was bound by its own MMA-issue loop (ncu: tensor pipe 39 % active, no memory unit above 15 %).
+    const uint64_t db_tpl = make_mn_desc(0, p.halo ? p.hb : BOX_BYTES);
+    uint64_t da_tpl[2];
+    da_tpl[0] = make_mn_desc(0, (1 < aboxes) ? BOX_BYTES : 0);
+    da_tpl[1] = make_mn_desc(0, (3 < aboxes) ? BOX_BYTES : 0);
+    const uint32_t tap_step = p.halo ? p.dil * 128 : nboxes * BOX_BYTES;      // bytes between the B bases of two taps
     for (int t = t0; t < t1; ++t) {
       mbar_wait(full0 + 8 * stage, phase);
       tc_fence_after();
       const uint32_t sa = smem_base + stage * stage_bytes;
       if (leader) {
-        for (int ti = 0; ti < ntap; ++ti) {
-          const uint32_t sb = sa + (aboxes + ti * nboxes) * BOX_BYTES;
-          for (int mt = 0; mt < mtiles; ++mt) {
+        uint32_t sb = sa + aboxes * BOX_BYTES;
+        uint32_t d_tmem = tmem_base;
+        const uint32_t acc0 = t > t0 ? 1u : 0u;
+        for (int ti = 0; ti < ntap; ++ti, sb += tap_step) {
+          const uint64_t db = db_tpl + (uint64_t)((sb & 0x3FFFF) >> 4);
+          for (int mt = 0; mt < mtiles; ++mt, d_tmem += ncols) {
+            const uint64_t da = da_tpl[mt] + (uint64_t)(((sa + mt * 2 * BOX_BYTES) & 0x3FFFF) >> 4);
+            umma_bf16(d_tmem, da, db, idesc, acc0);
 #pragma unroll
-            for (int k = 0; k < PK / 16; ++k) {
-              const uint64_t da = make_mn_desc(sa + mt * 2 * BOX_BYTES + k * 2048, (2 * mt + 1 < aboxes) ? BOX_BYTES : 0);
-              const uint64_t db = make_mn_desc(sb + k * 2048, BOX_BYTES);
-              umma_bf16(tmem_base + (ti * mtiles + mt) * ncols, da, db, idesc, (t > t0 || k > 0) ? 1u : 0u);
-            }
+            for (int k = 1; k < PK / 16; ++k) umma_bf16(d_tmem, da + (uint64_t)(k * 128), db + (uint64_t)(k * 128), idesc, 1u);
           }
         }
         umma_commit(empty0 + 8 * stage);
@@ -377,6 +398,10 @@ static int wg_plan(const HnConv* d, const PGeom& g, WgTc* pp) {
   if (tpj > taps) tpj = taps;
   p.tgroups = (taps + tpj - 1) / tpj;
   p.tpj = (taps + p.tgroups - 1) / p.tgroups;
+  p.halo = (d->KH == 3 && d->KW == 3 && d->stride == 1 && d->pad == d->dil && d->dil >= 1 && d->dil <= 4 && g.BW == PK &&
+            d->Cout <= 128 && d->C1 <= 128 && d->C2 <= 128) ? 1 : 0;
+  p.hb = ((PK + 2 * d->dil) * 128 + 1023) & ~1023;
+  if (p.halo) { p.tgroups = 3; p.tpj = 3; }
   const int jobs = p.mblocks * (p.ct1 + p.ct2) * p.tgroups;
   // one wave of 148 CTAs (one CTA per SM: 512 TMEM columns; measured: a second wave only doubles the
   // flush atomics): the largest split count that keeps jobs * splits <= 148, >= 8 pixel tiles per item
@@ -392,7 +417,7 @@ static int wg_plan(const HnConv* d, const PGeom& g, WgTc* pp) {
     const int ab = (rem + 63) / 64;
     const int c1 = d->C1 < 256 ? d->C1 : 256, c2 = d->C2 < 256 ? d->C2 : 256;
     const int nb = (c1 > c2 ? c1 : c2) / 64 * p.tpj;
-    int st = (192 * 1024) / ((ab + nb) * BOX_BYTES);
+    int st = p.halo ? (192 * 1024) / (ab * BOX_BYTES + (c1 > c2 ? c1 : c2) / 64 * p.hb) : (192 * 1024) / ((ab + nb) * BOX_BYTES);
     p.stages = st > WG_STAGES ? WG_STAGES : (st < 2 ? 2 : st);
   }
   return jobs;
@@ -421,16 +446,18 @@ extern "C" int hn_conv_wgrad_tc(const HnConv* d, const void* x1, const void* x2,
   PGeom g1 = g;
   int rc = make_map(&mdz, dy, d->B, d->OH, d->OW, d->Cout, d->ldy, g1, 1);
   if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(dz) = %d", rc);
-  rc = make_map(&mx1, x1, d->B, d->H, d->W, d->C1, d->ld1, g, d->stride);
+  WgTc p;
+  const int jobs = wg_plan(d, g, &p);
+  PGeom gx = g;
+  if (p.halo) gx.BW = PK + 2 * d->dil;            // one box = the 64 pixels of the step plus the row halo
+  rc = make_map(&mx1, x1, d->B, d->H, d->W, d->C1, d->ld1, gx, d->stride);
   if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(x1) = %d", rc);
   if (d->C2) {
-    rc = make_map(&mx2, x2, d->B, d->H, d->W, d->C2, d->ld2, g, d->stride);
+    rc = make_map(&mx2, x2, d->B, d->H, d->W, d->C2, d->ld2, gx, d->stride);
     if (rc) HN_FAIL(HN_ECUDA, "conv_wgrad_tc: cuTensorMapEncodeTiled(x2) = %d", rc);
   } else {
     mx2 = mx1;
   }
-  WgTc p;
-  const int jobs = wg_plan(d, g, &p);
   p.Creal = Creal;
   p.s_n = s_n; p.s_c = s_c; p.s_kh = s_kh; p.s_kw = s_kw; p.dw = dw;
   const int taps = d->KH * d->KW;
