@@ -296,6 +296,58 @@ def test_gradient_sink_two_backwards_per_zero_grad_accumulate():
     assert rel_l2(direct, plain) < 1e-3
 
 
+def test_weight_gradients_on_the_side_stream_match_the_serial_order():
+    """Sunk weight gradients run on a side stream and rejoin once, in an end-of-backward engine callback
+    (ops._conv_backward): the arena must hold the same gradients as with everything on one stream, the side stream must
+    be joined when backward() returns, and a backward that raises half-way must not leave it dangling."""
+    import hybridnet
+    from hybridnet import ops, parallel
+    torch.manual_seed(0)
+    # eval-mode BatchNorm: with batch statistics two runs of the SAME schedule already differ by percents at random
+    # initialisation (atomic summation order -> statistics -> bf16 rounding flips through 18 BatchNorm layers)
+    m = hybridnet.UNet(3, 1, init_features=32).cuda().eval()
+    arena = parallel.GradArena(m).direct(True)
+    x, y = torch.rand(4, 3, 128, 128).cuda(), (torch.rand(4, 1, 128, 128) > 0.5).float().cuda()
+    crit = hybridnet.DiceLoss()
+
+    def grads():
+        arena.zero_grad()
+        ops.begin_step(x.device, sum(p.numel() for p in m.parameters()) + (1 << 16))
+        crit(m(x), y).backward()
+        assert ops.deferred_side_stream() is None          # joined by the callback
+        torch.cuda.synchronize()
+        return arena.arena.clone()
+
+    try:
+        assert ops.WGRAD_OVERLAP and ops.WGRAD_DEFER
+        side = grads()
+        again = grads()
+        ops.WGRAD_OVERLAP = False
+        serial = grads()
+        ops.WGRAD_OVERLAP = True
+        assert rel_l2(side, serial) < 1e-3 and rel_l2(again, serial) < 1e-3
+
+        class Boom(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, t):
+                return t.clone()
+
+            @staticmethod
+            def backward(ctx, g):
+                raise RuntimeError("boom")
+        arena.zero_grad()
+        with pytest.raises(RuntimeError, match="boom"):
+            # the head's weight gradient is deferred first, then the failing node stops the pass
+            crit(m.conv(Boom.apply(torch.rand(4, 32, 128, 128, device="cuda", requires_grad=True))).sigmoid(), y).backward()
+        arena.zero_grad()                                    # start of the next step: rejoins whatever was left
+        assert ops.deferred_side_stream() is None
+        assert rel_l2(grads(), serial) < 1e-3
+    finally:
+        ops.WGRAD_OVERLAP = True
+        arena.direct(False)
+        ops.end_zero_pool()
+
+
 def test_pack_cache_keeps_buffers_across_weight_updates():
     from hybridnet import ops
     w = (torch.rand(64, 64, 3, 3).cuda() - 0.5).requires_grad_(True)

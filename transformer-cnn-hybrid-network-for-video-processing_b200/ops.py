@@ -92,6 +92,7 @@ def begin_step(device, capacity=None):
         zp["buf"] = torch.empty(int(capacity), dtype=torch.float32, device=device)
     zp["buf"].zero_()
     zp["off"], zp["live"] = 0, True
+    join_deferred()          # a backward pass that raised half-way never ran its end-of-pass callback
 
 
 def end_zero_pool():
@@ -588,6 +589,13 @@ def _defer_join(main, side, tensors):
         return False
     st["refs"].append(tensors)
     return True
+
+
+def join_deferred():
+    """Rejoin a side stream left over from a backward pass whose end-of-pass callback did not run (an exception inside
+    backward).  Called at the start of every step (begin_step, GradArena.zero_grad); a no-op otherwise."""
+    if _deferred["side"] is not None:
+        _join_deferred()
 
 
 def deferred_side_stream():

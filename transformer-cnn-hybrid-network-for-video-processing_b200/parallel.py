@@ -116,6 +116,8 @@ class GradArena:
 
     def zero_grad(self):
         """One memset instead of one per tensor; gradients stay views of the arena."""
+        from . import ops
+        ops.join_deferred()
         self.arena.zero_()
         self._attach()
         self.pending = list(self.bucket_size)
