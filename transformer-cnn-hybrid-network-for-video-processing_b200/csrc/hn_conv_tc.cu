@@ -537,6 +537,8 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
   } else if (warp == 1) {
     const bool leader = elect_one();
     const uint32_t sA_base = smem_u32(sA), sW_base = smem_u32(sWt);
+    const uint64_t desc_tpl = make_kmajor_desc_rows<ROWB>(0, 0);          // base_offset 0 (see make_kmajor_desc_rows)
+    const uint64_t a_tap_step = (uint64_t)((p.dil * ROWB) >> 4), b_tap_step = (uint64_t)((kit_tap * B_BYTES) >> 4);
     mbar_wait(wfull, 0);
     int stage = 0;
     uint32_t phase = 0;
@@ -553,14 +555,22 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_cons
           mbar_wait(full0 + 8 * stage, phase);
           tc_fence_after();
           const uint32_t sa = sA_base + stage * stage_bytes;
+          // descriptor templates + start-address offsets, computed OUTSIDE the elected region (warp-uniform code: the
+          // values stay in uniform registers; inside `if (leader)` every descriptor went through R2UR).  A tile of the
+          // C = 32 layers is 18 small MMAs, and building both descriptors from scratch for every tap kept the ONE issuing
+          // warp busy for most of a tile's ~2000 clocks (ncu: its instructions collected a full warp's share of samples).
+          uint64_t da[3], db[3];
+          da[0] = desc_tpl + (uint64_t)(sa >> 4);
+          db[0] = desc_tpl + (uint64_t)((sW_base + ((kh * 3) * kit_tap + kc) * B_BYTES) >> 4);
+          da[1] = da[0] + a_tap_step; da[2] = da[1] + a_tap_step;
+          db[1] = db[0] + b_tap_step; db[2] = db[1] + b_tap_step;
+          const uint32_t first_acc = rs > 0 ? 1u : 0u;
           if (leader) {
 #pragma unroll
             for (int kw = 0; kw < 3; ++kw) {
-              const uint64_t da = make_kmajor_desc_rows<ROWB>(sa + kw * p.dil * ROWB, base_off_mode);
-              const uint64_t db = make_kmajor_desc<ROWB>(sW_base + ((kh * 3 + kw) * kit_tap + kc) * B_BYTES);
 #pragma unroll
               for (int k = 0; k < BKC / 16; ++k)
-                umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), IDESC, (rs > 0 || kw > 0 || k > 0) ? 1u : 0u);
+                umma_bf16(d_tmem, da[kw] + (uint64_t)(k * 2), db[kw] + (uint64_t)(k * 2), IDESC, (kw > 0 || k > 0) ? 1u : first_acc);
             }
             umma_commit(empty0 + 8 * stage);
           }
