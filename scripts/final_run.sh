@@ -24,7 +24,8 @@ timeout -k 10 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1
   --log-file $O/ncu_launches_fct.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extra > $O/ncu.log 2>&1
 python scripts/ncu_launches.py $O/ncu_launches_fct.csv "FCT B=32: first 1400 launches of bench.py --steps 1 --warmup 3 --no-extra (about 2.5 steps)" > $O/ncu_launches_fct_summary.txt 2>&1
 # roofline.traffic: the dominant kernel of each workload at the bench shapes
-timeout -k 10 300 ncu --set full --clock-control none -k regex:attn_bwd_tc_kernel -c 1 -o $O/attn_bwd_d4 python scripts/ncu_attn.py 4 tc 32 > $O/ncu_attn4.log 2>&1
+timeout -k 10 300 ncu --set full --clock-control none -k regex:attn_bwd_tc_kernel -c 1 -o $O/attn_bwd_d4 python scripts/ncu_attn.py 4 tc 32 16384 > $O/ncu_attn4.log 2>&1
+timeout -k 10 300 ncu --set full --clock-control none -k regex:attn_bwd_tc_kernel -c 1 -o $O/attn_bwd_d8 python scripts/ncu_attn.py 8 tc 32 4096 > $O/ncu_attn8.log 2>&1
 cat $O/gpu_tests.log $O/smoke.log
 python - <<PY
 import json, glob

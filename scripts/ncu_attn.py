@@ -1,5 +1,5 @@
 """One small launch of each attention kernel for `ncu --set full` (keeps the replay count low).
-Usage: python scripts/ncu_attn.py [D] [tc] [B]   (B = 32 is the bench shape of FCT block 1 / 9)"""
+Usage: python scripts/ncu_attn.py [D] [tc] [B] [N]   (4 tc 32 16384 and 8 tc 32 4096 are the bench shapes of FCT blocks 1 / 9 and 2 / 8)"""
 import math
 import os
 import sys
@@ -10,7 +10,7 @@ import torch  # noqa: E402
 from hybridnet import _lib  # noqa: E402
 from hybridnet._lib import call  # noqa: E402
 
-B, N, heads, D = (int(sys.argv[3]) if len(sys.argv) > 3 else 4), 16384, 2, int(sys.argv[1]) if len(sys.argv) > 1 else 4
+B, N, heads, D = (int(sys.argv[3]) if len(sys.argv) > 3 else 4), (int(sys.argv[4]) if len(sys.argv) > 4 else 16384), 2, int(sys.argv[1]) if len(sys.argv) > 1 else 4
 C = heads * D
 dev = torch.device("cuda")
 q, k, v, do = [(torch.randn(B, N, C, device=dev) * 0.7).to(torch.bfloat16) for _ in range(4)]
