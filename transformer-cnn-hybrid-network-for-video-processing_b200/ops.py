@@ -457,19 +457,29 @@ def _wgrad_raw(x1, x2, dz, dw, *, Creal, OH, OW, Cout, KH, KW, stride, pad, dil,
 # ----------------------------------------------------------------------------
 # convolution (+bias +residual +activation), optionally followed by BatchNorm
 # ----------------------------------------------------------------------------
-def _act_bwd(dy, yz, act, want_dbias):
-    """dz = dy * act'(.) ; dbias = column sums of dz (fp32[Cp])."""
+def _act_bwd(dy, yz, act, want_dbias, bias=None):
+    """dz = dy * act'(.) ; dbias = column sums of dz (fp32[Cp]).  With `bias` (the parameter) and a gradient sink whose
+    slice has exactly the padded length, the sums are reduced straight into the arena: the function then returns
+    dbias = None and has already told the sink (no zero-pool slice, no AccumulateGrad add launch)."""
     dy, lddy = nhwc(dy)
     B, H, W, C = dy.shape
     P = B * H * W
-    dbias = _f32(C, dy) if want_dbias else None
+    dbias = None
+    sunk = None
+    if want_dbias:
+        sunk = _sink_for(bias) if (bias is not None and bias.numel() == C and bias.dtype == torch.float32) else None
+        dbias = sunk if sunk is not None else _f32(C, dy)
     if act == ACT_NONE:
         if want_dbias:
             call("hn_colsum", dy.data_ptr(), P, C, lddy, dbias.data_ptr(), _stream())
-        return dy, dbias
-    yz, ldy = nhwc(yz)
-    dz = _new(B, H, W, C, dy)
-    call("hn_act_bwd", dy.data_ptr(), yz.data_ptr(), dz.data_ptr(), P, C, lddy, ldy, C, act, _ptr(dbias), _stream())
+        dz = dy
+    else:
+        yz, ldy = nhwc(yz)
+        dz = _new(B, H, W, C, dy)
+        call("hn_act_bwd", dy.data_ptr(), yz.data_ptr(), dz.data_ptr(), P, C, lddy, ldy, C, act, _ptr(dbias), _stream())
+    if sunk is not None:
+        _sink_done(bias.data_ptr())
+        dbias = None
     return dz, dbias
 
 
@@ -684,6 +694,7 @@ class _ConvFn(torch.autograd.Function):
         y = _conv_forward(g, x1, x2, weight, bias, res, act)
         ctx.g, ctx.act = g, act
         ctx.has_bias, ctx.has_res = bias is not None, res is not None
+        ctx.bias = bias                       # the parameter itself (its address finds the gradient sink in backward)
         ctx.save_for_backward(x1, x2, weight, y if act != ACT_NONE else None)
         return y
 
@@ -692,7 +703,7 @@ class _ConvFn(torch.autograd.Function):
         x1, x2, weight, y = ctx.saved_tensors
         g = ctx.g
         need = ctx.needs_input_grad
-        dz, dbias = _act_bwd(dy, y, ctx.act, ctx.has_bias and need[3])
+        dz, dbias = _act_bwd(dy, y, ctx.act, ctx.has_bias and need[3], ctx.bias)
         dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2])
         if dbias is not None:
             dbias = dbias[: g.Cout]
@@ -1194,6 +1205,7 @@ class _LayerNormFn(torch.autograd.Function):
         call("hn_layernorm_fwd", x.data_ptr(), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), B * H * W, C, ld, C,
              eps, _stream())
         ctx.eps = eps
+        ctx.beta = beta
         ctx.save_for_backward(x, gamma)
         return y
 
@@ -1204,9 +1216,17 @@ class _LayerNormFn(torch.autograd.Function):
         dy, lddy = nhwc(dy)
         B, H, W, C = x.shape
         dx = _new(B, H, W, C, x)
-        dg, db = _f32(C, x), _f32(C, x)
+        # dgamma / dbeta straight into the gradient sink when there is one
+        kg = _sink_for(gamma) if gamma.dtype == torch.float32 else None
+        kb = _sink_for(ctx.beta) if (kg is not None and ctx.beta.dtype == torch.float32) else None
+        sunk = kg is not None and kb is not None
+        dg, db = (kg, kb) if sunk else (_f32(C, x), _f32(C, x))
         call("hn_layernorm_bwd", x.data_ptr(), dy.data_ptr(), dx.data_ptr(), gamma.data_ptr(), dg.data_ptr(),
              db.data_ptr(), B * H * W, C, ld, lddy, C, ctx.eps, _stream())
+        if sunk:
+            _sink_done(gamma.data_ptr())
+            _sink_done(ctx.beta.data_ptr())
+            return dx, None, None, None
         return dx, dg, db, None
 
 
