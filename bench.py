@@ -147,6 +147,7 @@ def _bn_work(P, C, passes):
 WORK = {
     # BatchNorm passes (bf16 tensors of P x C): arguments as in include/hybridnet.h
     "hn_bn_apply": lambda a: _bn_work(a[7], a[8], 3 if a[1] else 2),
+    "hn_bn_apply_train": lambda a: _bn_work(a[15], a[16], 3 if a[1] else 2),
     "hn_bn_relu_bwd_reduce": lambda a: _bn_work(a[6], a[7], 2),
     "hn_bn_relu_bwd_apply": lambda a: _bn_work(a[9], a[10], 3),
     "hn_bn_bwd_reduce": lambda a: _bn_work(a[6], a[7], 4 if a[3] else 3),

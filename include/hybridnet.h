@@ -177,6 +177,13 @@ int hn_bn_finalize(const float* sum, const float* sqsum, long long count, int C,
 int hn_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd,
                 const float* gamma, const float* beta, long long P, int C, int ldx, int ldr,
                 int ldy, int act, void* stream);
+/* hn_bn_finalize + hn_bn_apply in ONE launch (training): every CTA derives mean / rstd from the sums (count = pixels per
+ * channel), CTA 0 writes them to mean / rstd for the backward pass and updates running_mean / running_var (momentum,
+ * unbiased variance) and num_batches_tracked exactly as hn_bn_finalize does.  UNet.py:58-63, pyc:AE_32K Bottleneck. */
+int hn_bn_apply_train(const void* x, const void* res, void* y, const float* sum, const float* sqsum, long long count,
+                      float eps, float momentum, float* mean, float* rstd, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, const float* gamma, const float* beta, long long P, int C,
+                      int ldx, int ldr, int ldy, int act, void* stream);
 /* pass 1: dz = dy*act'(y) (written to dz), s1 += sum dz, s2 += sum dz*xhat      */
 int hn_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, const float* mean,
                      const float* rstd, long long P, int C, int lddy, int ldy, int ldx, int lddz,

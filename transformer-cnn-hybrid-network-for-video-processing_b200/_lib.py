@@ -61,6 +61,7 @@ SIGNATURES = {
     "hn_bn_stats": [_P, _L, _I, _I, _FP, _FP, _P],
     "hn_bn_finalize": [_FP, _FP, _L, _I, _F, _F, _FP, _FP, _FP, _FP, _P, _P],
     "hn_bn_apply": [_P, _P, _P, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _I, _I, _P],
+    "hn_bn_apply_train": [_P, _P, _P, _FP, _FP, _L, _F, _F, _FP, _FP, _FP, _FP, _P, _FP, _FP, _L, _I, _I, _I, _I, _I, _P],
     "hn_bn_bwd_reduce": [_P, _P, _P, _P, _FP, _FP, _L, _I, _I, _I, _I, _I, _I, _FP, _FP, _P],
     "hn_bn_bwd_apply": [_P, _P, _P, _FP, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _I, _I, _P],
     "hn_bn_relu_bwd_reduce": [_P, _P, _FP, _FP, _FP, _FP, _L, _I, _I, _I, _FP, _FP, _P],

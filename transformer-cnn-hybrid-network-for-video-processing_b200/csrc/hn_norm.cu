@@ -160,12 +160,51 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
 }
 // U pixels in flight per thread: 2 with a residual stream (64 B outstanding), 4 without -- with one input
 // stream two 16-byte loads per thread at 768 threads/SM left HBM3e under-subscribed (3.7 of ~5.5 TB/s).
-template <int U, bool RES>
+// FIN: the statistics pass is folded in (training): every CTA derives mean / rstd of all channels from the sums the conv
+// epilogue left (one channel per thread, the bn_finalize arithmetic in double) into shared memory; CTA 0 also writes them
+// out for the backward pass and moves the running statistics and num_batches_tracked.  One launch less per BatchNorm
+// layer (37 per Autoencoder32K step).
+struct BnFin {
+  const float* sum;
+  const float* sq;
+  long long count;
+  float eps, momentum;
+  float* mean_out;
+  float* rstd_out;
+  float* rmean;
+  float* rvar;
+  long long* num_batches;
+};
+template <int U, bool RES, bool FIN>
 __global__ void __launch_bounds__(256, 3) bn_apply_kernel(const bf16* __restrict__ x, const bf16* __restrict__ res,
                                                        bf16* __restrict__ y, const float* __restrict__ mean,
                                                        const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                        const float* __restrict__ beta, long long P, int C, int ldx,
-                                                       int ldr, int ldy, int act) {
+                                                       int ldr, int ldy, int act, const BnFin fin) {
+  extern __shared__ float s_ms[];      // FIN: [2][C] mean, rstd
+  if (FIN) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && fin.num_batches) *fin.num_batches += 1;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const double m = (double)fin.sum[c] / (double)fin.count;
+      double v = (double)fin.sq[c] / (double)fin.count - m * m;
+      if (v < 0) v = 0;
+      const float mf = (float)m, rf = (float)(1.0 / sqrt(v + (double)fin.eps));
+      s_ms[c] = mf;
+      s_ms[C + c] = rf;
+      if (blockIdx.x == 0) {
+        fin.mean_out[c] = mf;
+        fin.rstd_out[c] = rf;
+        if (fin.rmean) {
+          const double unb = fin.count > 1 ? v * (double)fin.count / (double)(fin.count - 1) : v;
+          fin.rmean[c] = (1.f - fin.momentum) * fin.rmean[c] + fin.momentum * mf;
+          fin.rvar[c] = (1.f - fin.momentum) * fin.rvar[c] + fin.momentum * (float)unb;
+        }
+      }
+    }
+    __syncthreads();
+    mean = s_ms;
+    rstd = s_ms + C;
+  }
   const int CV = C / 8;
   const ColIter it = col_iter(CV);
   float sc[8], sh[8];
@@ -347,9 +386,24 @@ extern "C" int hn_bn_finalize(const float* sum, const float* sqsum, long long co
 extern "C" int hn_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd, const float* gamma, const float* beta, long long P, int C, int ldx, int ldr, int ldy, int act, void* stream) {
   REQ_CV(C, "bn_apply");
   HN_REQUIRE(x && y && mean && rstd && gamma && beta, "bn_apply: null");
-  if (res) bn_apply_kernel<2, true><<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (const bf16*)res, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act);
-  else bn_apply_kernel<4, false><<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, nullptr, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act);
+  BnFin fin = {};
+  if (res) bn_apply_kernel<2, true, false><<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, (const bf16*)res, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act, fin);
+  else bn_apply_kernel<4, false, false><<<grid_bn(P * (C / 8)), TPB, 0, ST>>>((const bf16*)x, nullptr, (bf16*)y, mean, rstd, gamma, beta, P, C, ldx, ldr, ldy, act, fin);
   HN_CHECK_LAUNCH("bn_apply");
+  return HN_OK;
+}
+extern "C" int hn_bn_apply_train(const void* x, const void* res, void* y, const float* sum, const float* sqsum, long long count,
+                                 float eps, float momentum, float* mean, float* rstd, float* running_mean, float* running_var,
+                                 long long* num_batches_tracked, const float* gamma, const float* beta, long long P, int C,
+                                 int ldx, int ldr, int ldy, int act, void* stream) {
+  REQ_CV(C, "bn_apply_train");
+  HN_REQUIRE(x && y && sum && sqsum && mean && rstd && gamma && beta && count > 0, "bn_apply_train: null");
+  HN_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_apply_train: running stats come in pairs");
+  BnFin fin = {sum, sqsum, count, eps, momentum, mean, rstd, running_mean, running_var, num_batches_tracked};
+  const size_t smem = 2 * (size_t)C * sizeof(float);
+  if (res) bn_apply_kernel<2, true, true><<<grid_bn(P * (C / 8)), TPB, smem, ST>>>((const bf16*)x, (const bf16*)res, (bf16*)y, nullptr, nullptr, gamma, beta, P, C, ldx, ldr, ldy, act, fin);
+  else bn_apply_kernel<4, false, true><<<grid_bn(P * (C / 8)), TPB, smem, ST>>>((const bf16*)x, nullptr, (bf16*)y, nullptr, nullptr, gamma, beta, P, C, ldx, ldr, ldy, act, fin);
+  HN_CHECK_LAUNCH("bn_apply_train");
   return HN_OK;
 }
 extern "C" int hn_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, const float* mean, const float* rstd, long long P, int C, int lddy, int ldy, int ldx, int lddz, int act, float* s1, float* s2, void* stream) {

@@ -768,11 +768,6 @@ class _BnActFn(torch.autograd.Function):
             rm = rv = None
             if running_mean is not None:
                 rm, rv = _pad_vec(running_mean, Cp), _pad_vec(running_var, Cp, 1.0)
-            call("hn_bn_finalize", s0.data_ptr(), s1.data_ptr(), P, Cp, eps, momentum, mean.data_ptr(),
-                 rstd.data_ptr(), _ptr(rm), _ptr(rv), _ptr(count_real), _stream())
-            if rm is not None and rm.data_ptr() != running_mean.data_ptr():      # padded copies only (C % 8 != 0)
-                running_mean.copy_(rm[:C])
-                running_var.copy_(rv[:C])
         else:
             mean = _pad_vec(running_mean, Cp)
             rstd = torch.rsqrt(_pad_vec(running_var, Cp, 1.0) + eps)
@@ -780,8 +775,17 @@ class _BnActFn(torch.autograd.Function):
         ldr = 0
         if res is not None:
             res, ldr = nhwc(res)
-        call("hn_bn_apply", z.data_ptr(), _ptr(res), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gam.data_ptr(),
-             bet.data_ptr(), P, Cp, ldz, ldr, Cp, act, _stream())
+        if training:
+            # statistics -> mean / rstd / running statistics and the normalisation in one launch
+            call("hn_bn_apply_train", z.data_ptr(), _ptr(res), y.data_ptr(), s0.data_ptr(), s1.data_ptr(), P, eps, momentum,
+                 mean.data_ptr(), rstd.data_ptr(), _ptr(rm), _ptr(rv), _ptr(count_real), gam.data_ptr(), bet.data_ptr(),
+                 P, Cp, ldz, ldr, Cp, act, _stream())
+            if rm is not None and rm.data_ptr() != running_mean.data_ptr():      # padded copies only (C % 8 != 0)
+                running_mean.copy_(rm[:C])
+                running_var.copy_(rv[:C])
+        else:
+            call("hn_bn_apply", z.data_ptr(), _ptr(res), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gam.data_ptr(),
+                 bet.data_ptr(), P, Cp, ldz, ldr, Cp, act, _stream())
         ctx.act, ctx.training, ctx.C, ctx.has_res = act, training, C, res is not None
         direct = C == Cp and gamma.requires_grad and beta.requires_grad and gamma.dtype == torch.float32
         ctx.gptr, ctx.bptr = (gamma.data_ptr(), beta.data_ptr()) if direct else (0, 0)
