@@ -632,17 +632,17 @@ def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side):
     if side is not None:
         side.wait_stream(main)
     with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
-      if need_dw:
-        sunk = _sink_for(weight)
-        dw = sunk.view(weight.shape) if sunk is not None else _f32(tuple(weight.shape), weight)
-        if g.transposed:
-            # dW[ci][co][kh][kw] = sum_p x[p,ci] * dy[2p+(kh,kw), co]: wgrad of the k2s2 conv dy -> x
-            _wgrad_raw(dz, None, x1, dw, Creal=g.Cout, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
-                       dil=1, ups=0, strides=(g.Cout * 4, 4, 2, 1))
-        else:
-            _wgrad_raw(x1, x2, dz, dw, Creal=g.Cin, OH=g.OH, OW=g.OW, Cout=g.Cout, KH=g.KH, KW=g.KW,
-                       stride=g.stride, pad=g.pad, dil=g.dil, ups=g.ups,
-                       strides=(g.Cin * g.KH * g.KW, g.KH * g.KW, g.KW, 1), H=g.H, W=g.W)
+        if need_dw:
+            sunk = _sink_for(weight)
+            dw = sunk.view(weight.shape) if sunk is not None else _f32(tuple(weight.shape), weight)
+            if g.transposed:
+                # dW[ci][co][kh][kw] = sum_p x[p,ci] * dy[2p+(kh,kw), co]: wgrad of the k2s2 conv dy -> x
+                _wgrad_raw(dz, None, x1, dw, Creal=g.Cout, OH=g.H, OW=g.W, Cout=g.Cin, KH=2, KW=2, stride=2, pad=0,
+                           dil=1, ups=0, strides=(g.Cout * 4, 4, 2, 1))
+            else:
+                _wgrad_raw(x1, x2, dz, dw, Creal=g.Cin, OH=g.OH, OW=g.OW, Cout=g.Cout, KH=g.KH, KW=g.KW,
+                           stride=g.stride, pad=g.pad, dil=g.dil, ups=g.ups,
+                           strides=(g.Cin * g.KH * g.KW, g.KH * g.KW, g.KW, 1), H=g.H, W=g.W)
     if need_dx:
         if g.transposed:
             wp, Kpad = _packed(weight, "tdgrad", dz.shape[3])
