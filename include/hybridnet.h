@@ -206,19 +206,22 @@ int hn_bn_relu_bwd_apply(const void* dy, const void* x, void* dx, const float* m
 
 /* ---- conv-projected attention (FCT.py:24-79) -------------------------------- */
 /* q,k,v = LayerNorm_C(ReLU(dwconv3x3(x)+b)) for the three projections in one pass.
- * w: [3][C][9] fp32, b: [3][C], gamma/beta: [3][C]; out: [3] tensors of [P,C]   */
-int hn_dwconv_relu_ln_fwd(const void* x, void* q, void* k, void* v, const float* w, const float* b,
-                          const float* gamma, const float* beta, int B, int H, int W, int C,
+ * w, b, gamma, beta: HOST arrays of three device pointers (q, k, v) to the reference's own parameter tensors
+ * (conv_q/k/v.weight [C,1,3,3] fp32, .bias [C] -- the array or its entries may be null --, layernorm_q/k/v.weight /
+ * .bias [C]); out: [3] tensors of [P,C]                                                            */
+int hn_dwconv_relu_ln_fwd(const void* x, void* q, void* k, void* v, const float* const* w, const float* const* b,
+                          const float* const* gamma, const float* const* beta, int B, int H, int W, int C,
                           int ldx, int ldo, float eps, void* stream);
-/* backward: dpre[3] (grad at the dwconv output, after LN+ReLU backward), += dgamma/dbeta/db */
+/* backward: dpre[3] (grad at the dwconv output, after LN+ReLU backward), += dgamma/dbeta/db (arrays of three fp32 [C]
+ * accumulation targets, e.g. slices of a gradient arena; db may be null)                            */
 int hn_dwconv_relu_ln_bwd_pre(const void* x, const void* dq, const void* dk, const void* dv,
-                              void* dpre_q, void* dpre_k, void* dpre_v, const float* w,
-                              const float* b, const float* gamma, float* dgamma, float* dbeta,
-                              float* db, int B, int H, int W, int C, int ldx, int ldd, float eps,
-                              void* stream);
-/* dx = sum_t dwconv^T(dpre_t, w_t);  dw[3][C][9] += sum_p dpre_t[p,c] * x[p@tap,c] */
+                              void* dpre_q, void* dpre_k, void* dpre_v, const float* const* w,
+                              const float* const* b, const float* const* gamma, float* const* dgamma,
+                              float* const* dbeta, float* const* db, int B, int H, int W, int C, int ldx, int ldd,
+                              float eps, void* stream);
+/* dx = sum_t dwconv^T(dpre_t, w_t);  dw[t][C][9] += sum_p dpre_t[p,c] * x[p@tap,c]  (three targets) */
 int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpre_k,
-                              const void* dpre_v, void* dx, const float* w, float* dw, int B, int H,
+                              const void* dpre_v, void* dx, const float* const* w, float* const* dw, int B, int H,
                               int W, int C, int ldx, int ldd, int lddx, void* stream);
 /* softmax(Q K^T * scale) V per head, flash style.  q,k,v,o: [B,N,heads*D] with
  * pixel strides ld*; lse: fp32 [B,heads,N] (log-sum-exp, natural log).

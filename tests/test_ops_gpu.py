@@ -402,25 +402,27 @@ def test_maxpool_dropout_add_gelu3_layernorm(ops):
 def test_dwconv_relu_ln_qkv(ops, C):
     B, H = 2, 12
     x = _rand(B, C, H, H, seed=1).requires_grad_(True)
-    w = _rand(3, C, 9, seed=2, scale=0.4).requires_grad_(True)
-    b = _rand(3, C, seed=3, scale=0.2).requires_grad_(True)
-    g = (_rand(3, C, seed=4) * 0.5 + 1).requires_grad_(True)
-    be = (_rand(3, C, seed=5) * 0.2).requires_grad_(True)
+    # the reference's twelve separate parameter tensors: conv_{q,k,v}.weight [C,1,3,3] / .bias, layernorm_{q,k,v}.weight / .bias
+    w = [_rand(C, 1, 3, 3, seed=20 + t, scale=0.4).requires_grad_(True) for t in range(3)]
+    b = [_rand(C, seed=30 + t, scale=0.2).requires_grad_(True) for t in range(3)]
+    g = [(_rand(C, seed=40 + t) * 0.5 + 1).requires_grad_(True) for t in range(3)]
+    be = [(_rand(C, seed=50 + t) * 0.2).requires_grad_(True) for t in range(3)]
+    leaves = [x] + w + b + g + be
     refs = []
     for t in range(3):
-        y = F.relu(F.conv2d(x, w[t].view(C, 1, 3, 3), b[t], 1, 1, 1, C))
+        y = F.relu(F.conv2d(x, w[t], b[t], 1, 1, 1, C))
         refs.append(F.layer_norm(y.permute(0, 2, 3, 1), (C,), g[t], be[t], 1e-5).permute(0, 3, 1, 2))
     gys = [_rand(*refs[0].shape, seed=6 + t) for t in range(3)]
     torch.autograd.backward(refs, gys)
-    want = [t.grad.clone() for t in (x, w, b, g, be)]
-    for t in (x, w, b, g, be):
+    want = [t.grad.clone() for t in leaves]
+    for t in leaves:
         t.grad = None
-    outs = ops.dwconv_relu_ln_qkv(ops.to_nhwc(x), w, b, g, be)
+    outs = ops.dwconv_relu_ln_qkv(ops.to_nhwc(x), tuple(w), tuple(b), tuple(g), tuple(be))
     outs = [ops.to_nchw(o, C) for o in outs]
     for o, r in zip(outs, refs):
         assert rel_l2(o, r) < FWD_TOL
     torch.autograd.backward(outs, gys)
-    for t, r in zip((x, w, b, g, be), want):
+    for t, r in zip(leaves, want):
         assert rel_l2(t.grad, r) < 1.5e-2
 
 

@@ -42,21 +42,11 @@ class Attention(nn.Module):
         self.relu = nn.ReLU()
         self.dropout = nn.Dropout()          # constructed but unused in the reference too (FCT.py:39,78)
 
-    def _stacked(self):
+    def forward_conv_nhwc(self, x):
         convs = (self.conv_q, self.conv_k, self.conv_v)
         lns = (self.layernorm_q, self.layernorm_k, self.layernorm_v)
-        C = self._out_channels
-        w = torch.stack([c.weight.reshape(C, 9) for c in convs])
-        if convs[0].bias is not None:
-            b = torch.stack([c.bias for c in convs])
-        else:
-            b = torch.zeros(3, C, device=w.device)
-        g = torch.stack([l.weight for l in lns])
-        be = torch.stack([l.bias for l in lns])
-        return w, b, g, be
-
-    def forward_conv_nhwc(self, x):
-        return ops.dwconv_relu_ln_qkv(x, *self._stacked(), 1e-5)
+        return ops.dwconv_relu_ln_qkv(x, tuple(c.weight for c in convs), tuple(c.bias for c in convs),
+                                      tuple(l.weight for l in lns), tuple(l.bias for l in lns), 1e-5)
 
     def nhwc(self, x):
         q, k, v = self.forward_conv_nhwc(x)

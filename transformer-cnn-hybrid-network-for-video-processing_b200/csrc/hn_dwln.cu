@@ -33,9 +33,15 @@ __device__ __forceinline__ void dw_pre(const bf16* __restrict__ x, int b, int h,
   }
 }
 
+// The three projections' parameters are the reference's separate tensors (conv_q/k/v.weight [C,1,3,3], .bias [C],
+// layernorm_q/k/v.weight/.bias [C]): three pointers per kind instead of one stacked copy (the host used to torch.stack
+// them every forward and autograd unbound the stacked gradients again: ~28 at:: launches per attention layer).
+struct C3 { const float* p[3]; };
+struct M3 { float* p[3]; };
+
 __global__ void dwln_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ q, bf16* __restrict__ k, bf16* __restrict__ v,
-                                const float* __restrict__ w, const float* __restrict__ bias, const float* __restrict__ gamma,
-                                const float* __restrict__ beta, int B, int H, int W, int C, int ldx, int ldo, float eps) {
+                                const C3 w, const C3 bias, const C3 gamma, const C3 beta, int B, int H, int W, int C, int ldx,
+                                int ldo, float eps) {
   extern __shared__ float sm[];          // w: [3][9][C], b,gamma,beta: [3][C] each
   float* sw = sm;
   float* sb = sm + 27 * C;
@@ -43,9 +49,14 @@ __global__ void dwln_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ q
   float* sbe = sg + 3 * C;
   for (int i = threadIdx.x; i < 27 * C; i += blockDim.x) {
     int t = i / (9 * C), r = i % (9 * C), tap = r / C, c = r % C;
-    sw[i] = w[(t * C + c) * 9 + tap];
+    sw[i] = w.p[t][c * 9 + tap];
   }
-  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) { sb[i] = bias[i]; sg[i] = gamma[i]; sbe[i] = beta[i]; }
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const int t = i / C, c = i - t * C;
+    sb[i] = bias.p[t] ? bias.p[t][c] : 0.f;
+    sg[i] = gamma.p[t][c];
+    sbe[i] = beta.p[t][c];
+  }
   __syncthreads();
   const int CV = C / 8;
   const long long P = (long long)B * H * W;
@@ -83,17 +94,16 @@ __global__ void dwln_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ q
 // grid.y = projection t
 __global__ void dwln_bwd_pre_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dq, const bf16* __restrict__ dk,
                                     const bf16* __restrict__ dv, bf16* __restrict__ pq, bf16* __restrict__ pk,
-                                    bf16* __restrict__ pv, const float* __restrict__ w, const float* __restrict__ bias,
-                                    const float* __restrict__ gamma, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                    float* __restrict__ db, int B, int H, int W, int C, int ldx, int ldd, float eps) {
+                                    bf16* __restrict__ pv, const C3 w, const C3 bias, const C3 gamma, const M3 dgamma,
+                                    const M3 dbeta, const M3 db, int B, int H, int W, int C, int ldx, int ldd, float eps) {
   extern __shared__ float sm[];          // w [9][C], b [C], gamma [C], acc [3][C]
   const int t = blockIdx.y;
   float* sw = sm;
   float* sb = sm + 9 * C;
   float* sg = sb + C;
   float* sacc = sg + C;
-  for (int i = threadIdx.x; i < 9 * C; i += blockDim.x) { int tap = i / C, c = i % C; sw[i] = w[(t * C + c) * 9 + tap]; }
-  for (int i = threadIdx.x; i < C; i += blockDim.x) { sb[i] = bias[t * C + i]; sg[i] = gamma[t * C + i]; }
+  for (int i = threadIdx.x; i < 9 * C; i += blockDim.x) { int tap = i / C, c = i % C; sw[i] = w.p[t][c * 9 + tap]; }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) { sb[i] = bias.p[t] ? bias.p[t][i] : 0.f; sg[i] = gamma.p[t][i]; }
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sacc[i] = 0.f;
   __syncthreads();
   const bf16* dys = t == 0 ? dq : (t == 1 ? dk : dv);
@@ -151,24 +161,24 @@ __global__ void dwln_bwd_pre_kernel(const bf16* __restrict__ x, const bf16* __re
   col_fold8(sacc + 2 * C, apb, cv, CV);
   __syncthreads();
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(dgamma + t * C + i, sacc[i]);
-    atomicAdd(dbeta + t * C + i, sacc[C + i]);
-    atomicAdd(db + t * C + i, sacc[2 * C + i]);
+    atomicAdd(dgamma.p[t] + i, sacc[i]);
+    atomicAdd(dbeta.p[t] + i, sacc[C + i]);
+    if (db.p[t]) atomicAdd(db.p[t] + i, sacc[2 * C + i]);
   }
 }
 
 // thread = (pixel, channel pair): dx and 3x9x2 weight-gradient partials in registers
 __global__ void __launch_bounds__(TPB) dw_bwd_dw_kernel(const bf16* __restrict__ x, const bf16* __restrict__ pq,
                                                         const bf16* __restrict__ pk, const bf16* __restrict__ pv,
-                                                        bf16* __restrict__ dx, const float* __restrict__ w,
-                                                        float* __restrict__ dw, int B, int H, int W, int C, int ldx,
+                                                        bf16* __restrict__ dx, const C3 w, const M3 dw, int B, int H, int W,
+                                                        int C, int ldx,
                                                         int ldd, int lddx) {
   extern __shared__ float sm[];          // w [3][9][C], acc [3][9][C]
   float* sw = sm;
   float* sacc = sm + 27 * C;
   for (int i = threadIdx.x; i < 27 * C; i += blockDim.x) {
     int t = i / (9 * C), r = i % (9 * C), tap = r / C, c = r % C;
-    sw[i] = w[(t * C + c) * 9 + tap];
+    sw[i] = w.p[t][c * 9 + tap];
     sacc[i] = 0.f;
   }
   __syncthreads();
@@ -222,7 +232,7 @@ __global__ void __launch_bounds__(TPB) dw_bwd_dw_kernel(const bf16* __restrict__
   __syncthreads();
   for (int i = threadIdx.x; i < 27 * C; i += blockDim.x) {
     int t = i / (9 * C), r = i % (9 * C), tap = r / C, c = r % C;
-    atomicAdd(dw + (t * C + c) * 9 + tap, sacc[i]);
+    atomicAdd(dw.p[t] + c * 9 + tap, sacc[i]);
   }
 }
 }  // namespace
@@ -239,42 +249,51 @@ static int dwln_grid(long long items) {
   return (int)b;
 }
 
-extern "C" int hn_dwconv_relu_ln_fwd(const void* x, void* q, void* k, void* v, const float* w, const float* b,
-                                     const float* gamma, const float* beta, int B, int H, int W, int C, int ldx,
+static C3 c3(const float* const* a) { C3 r; for (int t = 0; t < 3; ++t) r.p[t] = a ? a[t] : nullptr; return r; }
+static M3 m3(float* const* a) { M3 r; for (int t = 0; t < 3; ++t) r.p[t] = a ? a[t] : nullptr; return r; }
+static bool all3(const float* const* a) { return a && a[0] && a[1] && a[2]; }
+
+// w / b / gamma / beta (and the gradient targets): HOST arrays of three device pointers, one per projection (q, k, v) --
+// the reference's own parameter tensors; b may be null (conv bias=False), as may db
+extern "C" int hn_dwconv_relu_ln_fwd(const void* x, void* q, void* k, void* v, const float* const* w, const float* const* b,
+                                     const float* const* gamma, const float* const* beta, int B, int H, int W, int C, int ldx,
                                      int ldo, float eps, void* stream) {
   if (int rc = dwln_check(C)) return rc;
-  HN_REQUIRE(x && q && k && v && w && b && gamma && beta, "dwconv_relu_ln_fwd: null");
+  HN_REQUIRE(x && q && k && v && all3(w) && all3(gamma) && all3(beta), "dwconv_relu_ln_fwd: null");
   size_t smem = (27 + 9) * C * sizeof(float);
   dwln_fwd_kernel<<<dwln_grid((long long)B * H * W * (C / 8)), TPB, smem, ST>>>(
-      (const bf16*)x, (bf16*)q, (bf16*)k, (bf16*)v, w, b, gamma, beta, B, H, W, C, ldx, ldo, eps);
+      (const bf16*)x, (bf16*)q, (bf16*)k, (bf16*)v, c3(w), c3(b), c3(gamma), c3(beta), B, H, W, C, ldx, ldo, eps);
   HN_CHECK_LAUNCH("dwln_fwd");
   return HN_OK;
 }
 extern "C" int hn_dwconv_relu_ln_bwd_pre(const void* x, const void* dq, const void* dk, const void* dv, void* dpre_q,
-                                         void* dpre_k, void* dpre_v, const float* w, const float* b,
-                                         const float* gamma, float* dgamma, float* dbeta, float* db, int B, int H,
-                                         int W, int C, int ldx, int ldd, float eps, void* stream) {
+                                         void* dpre_k, void* dpre_v, const float* const* w, const float* const* b,
+                                         const float* const* gamma, float* const* dgamma, float* const* dbeta,
+                                         float* const* db, int B, int H, int W, int C, int ldx, int ldd, float eps,
+                                         void* stream) {
   if (int rc = dwln_check(C)) return rc;
-  HN_REQUIRE(x && dq && dk && dv && dpre_q && dpre_k && dpre_v && w && b && gamma && dgamma && dbeta && db, "dwconv_relu_ln_bwd_pre: null");
+  HN_REQUIRE(x && dq && dk && dv && dpre_q && dpre_k && dpre_v && all3(w) && all3(gamma) && all3((const float* const*)dgamma) &&
+                 all3((const float* const*)dbeta),
+             "dwconv_relu_ln_bwd_pre: null");
   size_t smem = (9 + 2 + 3) * C * sizeof(float);
   dim3 grid(dwln_grid((long long)B * H * W * (C / 8)), 3);
   dwln_bwd_pre_kernel<<<grid, TPB, smem, ST>>>((const bf16*)x, (const bf16*)dq, (const bf16*)dk, (const bf16*)dv,
-                                               (bf16*)dpre_q, (bf16*)dpre_k, (bf16*)dpre_v, w, b, gamma, dgamma, dbeta,
-                                               db, B, H, W, C, ldx, ldd, eps);
+                                               (bf16*)dpre_q, (bf16*)dpre_k, (bf16*)dpre_v, c3(w), c3(b), c3(gamma), m3(dgamma),
+                                               m3(dbeta), m3(db), B, H, W, C, ldx, ldd, eps);
   HN_CHECK_LAUNCH("dwln_bwd_pre");
   return HN_OK;
 }
 extern "C" int hn_dwconv_bwd_data_weight(const void* x, const void* dpre_q, const void* dpre_k, const void* dpre_v,
-                                         void* dx, const float* w, float* dw, int B, int H, int W, int C, int ldx,
+                                         void* dx, const float* const* w, float* const* dw, int B, int H, int W, int C, int ldx,
                                          int ldd, int lddx, void* stream) {
   if (int rc = dwln_check(C)) return rc;
-  HN_REQUIRE(x && dpre_q && dpre_k && dpre_v && dx && w && dw, "dwconv_bwd_data_weight: null");
+  HN_REQUIRE(x && dpre_q && dpre_k && dpre_v && dx && all3(w) && all3((const float* const*)dw), "dwconv_bwd_data_weight: null");
   size_t smem = 54 * C * sizeof(float);
   long long items = (long long)B * H * W * (C / 2);
   int grid = dwln_grid(items);
   // total threads must be a multiple of C/2 so each thread keeps one channel pair
   dw_bwd_dw_kernel<<<grid, TPB, smem, ST>>>((const bf16*)x, (const bf16*)dpre_q, (const bf16*)dpre_k,
-                                            (const bf16*)dpre_v, (bf16*)dx, w, dw, B, H, W, C, ldx, ldd, lddx);
+                                            (const bf16*)dpre_v, (bf16*)dx, c3(w), m3(dw), B, H, W, C, ldx, ldd, lddx);
   HN_CHECK_LAUNCH("dw_bwd_dw");
   return HN_OK;
 }

@@ -1242,41 +1242,71 @@ def layernorm_c(x, gamma, beta, eps=1e-5):
 # ----------------------------------------------------------------------------
 # conv-projected attention (FCT.py:24-79)
 # ----------------------------------------------------------------------------
+def _p3(a, b, c):
+    """HOST array of three device pointers (None -> null) for the per-projection parameter arguments."""
+    import ctypes
+    return (ctypes.c_void_p * 3)(*(t.data_ptr() if t is not None else None for t in (a, b, c)))
+
+
 class _DwLnQKVFn(torch.autograd.Function):
-    """q,k,v = LayerNorm_C(ReLU(depthwise3x3(x))) for the three projections, one pass over x."""
+    """q,k,v = LayerNorm_C(ReLU(depthwise3x3(x))) for the three projections, one pass over x.  The parameters are the
+    reference's twelve separate tensors (conv_{q,k,v}.weight/.bias, layernorm_{q,k,v}.weight/.bias): the kernels take
+    three pointers per kind, and each parameter gradient is reduced straight into the gradient sink when there is one."""
 
     @staticmethod
-    def forward(ctx, x, w, b, gamma, beta, eps):
-        # w [3,C,9], b/gamma/beta [3,C] fp32 (stacked from conv_{q,k,v} / layernorm_{q,k,v})
+    def forward(ctx, x, eps, *params):
+        # params: wq, wk, wv [C,1,3,3]; bq, bk, bv [C] or None; gq, gk, gv; beq, bek, bev  (fp32)
         x, ld = nhwc(x)
         B, H, W, C = x.shape
+        w, b, g, be = params[0:3], params[3:6], params[6:9], params[9:12]
         qkv = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=x.device)
         call("hn_dwconv_relu_ln_fwd", x.data_ptr(), qkv[0].data_ptr(), qkv[1].data_ptr(), qkv[2].data_ptr(),
-             w.data_ptr(), b.data_ptr(), gamma.data_ptr(), beta.data_ptr(), B, H, W, C, ld, C, eps, _stream())
+             _p3(*w), _p3(*b), _p3(*g), _p3(*be), B, H, W, C, ld, C, eps, _stream())
         ctx.eps = eps
-        ctx.save_for_backward(x, w, b, gamma)
+        ctx.params = params
+        ctx.save_for_backward(x)
         return qkv[0], qkv[1], qkv[2]
 
     @staticmethod
     def backward(ctx, dq, dk, dv):
-        x, w, b, gamma = ctx.saved_tensors
+        (x,) = ctx.saved_tensors
+        params = ctx.params
+        w, b, g, be = params[0:3], params[3:6], params[6:9], params[9:12]
         x, ld = nhwc(x)
         B, H, W, C = x.shape
         dq, dk, dv = dq.contiguous(), dk.contiguous(), dv.contiguous()
         dpre = torch.empty((3, B, H, W, C), dtype=torch.bfloat16, device=x.device)
-        dgam, dbet, dbias = _f32((3, C), x), _f32((3, C), x), _f32((3, C), x)
+        # gradient targets: the sink's arena slice where there is one, zero-pool scratch otherwise
+        tgt, sunk = [], []
+        for t in params:
+            if t is None:
+                tgt.append(None); sunk.append(False)
+                continue
+            k = _sink_for(t) if (t.dtype == torch.float32 and t.requires_grad) else None
+            sunk.append(k is not None)
+            tgt.append(k if k is not None else _f32(t.numel(), x))
+        dw, db, dg, dbe = tgt[0:3], tgt[3:6], tgt[6:9], tgt[9:12]
         call("hn_dwconv_relu_ln_bwd_pre", x.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
-             dpre[0].data_ptr(), dpre[1].data_ptr(), dpre[2].data_ptr(), w.data_ptr(), b.data_ptr(), gamma.data_ptr(),
-             dgam.data_ptr(), dbet.data_ptr(), dbias.data_ptr(), B, H, W, C, ld, C, ctx.eps, _stream())
+             dpre[0].data_ptr(), dpre[1].data_ptr(), dpre[2].data_ptr(), _p3(*w), _p3(*b), _p3(*g), _p3(*dg), _p3(*dbe),
+             _p3(*db), B, H, W, C, ld, C, ctx.eps, _stream())
         dx = _new(B, H, W, C, x)
-        dw = _f32((3, C, 9), x)
         call("hn_dwconv_bwd_data_weight", x.data_ptr(), dpre[0].data_ptr(), dpre[1].data_ptr(), dpre[2].data_ptr(),
-             dx.data_ptr(), w.data_ptr(), dw.data_ptr(), B, H, W, C, ld, C, C, _stream())
-        return dx, dw, dbias, dgam, dbet, None
+             dx.data_ptr(), _p3(*w), _p3(*dw), B, H, W, C, ld, C, C, _stream())
+        grads = []
+        for t, k, s in zip(params, tgt, sunk):
+            if t is None:
+                grads.append(None)
+            elif s:
+                _sink_done(t.data_ptr())
+                grads.append(None)
+            else:
+                grads.append(k.view(t.shape))
+        return (dx, None, *grads)
 
 
-def dwconv_relu_ln_qkv(x, w, b, gamma, beta, eps=1e-5):
-    return _DwLnQKVFn.apply(x, w, b, gamma, beta, eps)
+def dwconv_relu_ln_qkv(x, weights, biases, gammas, betas, eps=1e-5):
+    """weights / biases / gammas / betas: 3-tuples (q, k, v) of the modules' parameters (biases may hold None)."""
+    return _DwLnQKVFn.apply(x, eps, *weights, *biases, *gammas, *betas)
 
 
 # tcgen05 / TMEM / TMA attention for the exponential-bound shapes (D in {4, 8}, two heads, N % 128 == 0: FCT blocks
