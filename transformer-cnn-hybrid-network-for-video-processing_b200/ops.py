@@ -529,7 +529,7 @@ def set_grad_sink(sink, done):
 
 def _sink_for(t):
     f = _grad_sink["sink"]
-    return f(t.data_ptr(), t.numel()) if (f is not None and t is not None) else None
+    return f(t.data_ptr(), t.numel()) if (f is not None and t is not None and t.is_contiguous()) else None
 
 
 def _sink_for_ptr(ptr, numel):

@@ -8,6 +8,8 @@ stream, so the exchange overlaps the rest of backward; ``finish()`` joins the st
 scales by 1/world.  BatchNorm statistics stay per-rank (what DDP gives; the reference has no
 SyncBN).
 """
+import bisect
+
 import torch
 import torch.distributed as dist
 
@@ -63,6 +65,8 @@ class GradArena:
         self._written = set()         # parameters whose gradient a kernel already reduced into the arena this step
         self._counted = set()         # parameters already counted towards their bucket this step
         self._rewritten = set()       # sunk parameters that were asked for a second time this step (scratch + autograd)
+        self._full, self._parts = set(), set()        # whole parameters / (parameter, offset) parts handed to a kernel
+        self._open, self._landed = {}, {}             # address -> (parameter, elements) in flight; elements done per parameter
         self._attach()
         self._hooks = [self._make_hook(i) for i in range(len(self.params))]
         if self.world > 1:
@@ -74,6 +78,8 @@ class GradArena:
         """Refresh the parameter-address table (after the parameters' storage moved, e.g. optim.AdamW re-pointing
         them into its flat buffer)."""
         self._by_ptr = {p.data_ptr(): i for i, p in enumerate(self.params)}
+        self._spans = sorted((p.data_ptr(), p.numel() * p.element_size(), i) for i, p in enumerate(self.params))
+        self._span_starts = [a for a, _, _ in self._spans]
 
     def direct(self, on=True):
         """Let the kernels reduce weight / BatchNorm-parameter gradients straight into the arena
@@ -90,21 +96,37 @@ class GradArena:
             # result, which is only right while the slice still holds the zeros of ``zero_grad``.  A second write
             # in the same step (gradient accumulation over micro-batches, a second backward, a module applied
             # twice) therefore gets None: that call reduces into scratch and autograd accumulates it.
-            i = self._by_ptr.get(ptr)
+            i, off = self._by_ptr.get(ptr), 0
             if i is None:
+                # a contiguous PART of a parameter: the q / k / v thirds of nn.MultiheadAttention's packed in_proj_weight
+                # and in_proj_bias reach the kernels as views
+                k = bisect.bisect_right(self._span_starts, ptr) - 1
+                if k < 0:
+                    return None
+                a, nbytes, i = self._spans[k]
+                if ptr + 4 * numel > a + nbytes or (ptr - a) % 4:
+                    return None
+                off = (ptr - a) // 4
+            s, e = self.slices[i]
+            if off + numel > e - s:
                 return None
-            if i in self._written:
+            part = numel != e - s
+            if (i in self._written and not part) or (i, off) in self._parts or (part and i in self._full):
                 self._rewritten.add(i)
                 return None
-            s, e = self.slices[i]
-            if e - s != numel:
-                return None
             self._written.add(i)
-            return self.arena[s:e]
+            if part:
+                self._parts.add((i, off))
+            else:
+                self._full.add(i)
+            self._open[ptr] = (i, numel)
+            return self.arena[s + off:s + off + numel]
 
         def done(ptr):
-            i = self._by_ptr[ptr]
-            if self.world > 1:
+            i, numel = self._open.pop(ptr)
+            self._landed[i] = self._landed.get(i, 0) + numel
+            s, e = self.slices[i]
+            if self._landed[i] == e - s and self.world > 1:      # every part of the parameter has been reduced
                 self._hooks[i](None)
 
         ops.set_grad_sink(sink, done)
@@ -125,6 +147,10 @@ class GradArena:
         self._written.clear()
         self._counted.clear()
         self._rewritten.clear()
+        self._full.clear()
+        self._parts.clear()
+        self._open.clear()
+        self._landed.clear()
 
     def _make_hook(self, i):
         def hook(_p):
