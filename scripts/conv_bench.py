@@ -1,5 +1,5 @@
 """Micro-benchmark of single conv launches through the C ABI (forward-type calls and weight gradients).
-  python scripts/conv_bench.py [--only SUBSTR] [--reps N]
+  python scripts/conv_bench.py [--only SUBSTR[,SUBSTR...]] [--reps N]
 Rotates over enough input/output buffers that every launch misses the 126 MB L2."""
 import argparse, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -43,6 +43,7 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--wgrad", action="store_true")
     ap.add_argument("--nostats", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="time the launches inside one CUDA graph")
     ap.add_argument("--lib", default="", help="a variant library built by scripts/attn_variants.sh")
     a = ap.parse_args()
     if a.lib:
@@ -53,7 +54,7 @@ def main():
     torch.manual_seed(0)
     print(f"{'geometry':22s} {'kernel':18s} {'us':>9s} {'TFLOP/s':>9s} {'GB/s':>8s}")
     for tag, B, H, W, C1, C2, Cout, k, s, dil, pshuf, st in GEOMS:
-        if a.only and a.only not in tag:
+        if a.only and not any(o in tag for o in a.only.split(",")):
             continue
         OH, OW = H // s, W // s
         st = st and not a.nostats
@@ -88,7 +89,22 @@ def main():
             run(i)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        if a.wgrad:       # exclude the zero-fill: time each launch separately
+        if a.wgrad and a.graph:    # accumulate into one dW inside a CUDA graph (no zero-fill, no host launch floor)
+            dwg = torch.zeros(Cout, C1 + C2, k, k, device=dev)
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                for i in range(a.reps):
+                    j = i % nbuf
+                    ops._wgrad_raw(xs[j], x2[j] if x2 else None, outs[j], dwg, Creal=C1 + C2, OH=OH, OW=OW, Cout=Cout, KH=k,
+                                   KW=k, stride=s, pad=pad, dil=dil, ups=0, strides=dwg.stride())
+            gr.replay()
+            torch.cuda.synchronize()
+            e0.record()
+            gr.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) / a.reps * 1e3
+        elif a.wgrad:     # exclude the zero-fill: time each launch separately
             tot = 0.0
             for i in range(a.reps):
                 j = i % nbuf
@@ -100,6 +116,18 @@ def main():
                 torch.cuda.synchronize()
                 tot += e0.elapsed_time(e1)
             us = tot / a.reps * 1e3
+        elif a.graph:     # the launches of one CUDA graph: no host launch floor (~20 us per call from Python) between them
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                for i in range(a.reps):
+                    run(i)
+            gr.replay()
+            torch.cuda.synchronize()
+            e0.record()
+            gr.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) / a.reps * 1e3
         else:
             e0.record()
             for i in range(a.reps):

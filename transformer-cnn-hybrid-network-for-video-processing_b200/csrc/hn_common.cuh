@@ -29,7 +29,22 @@ void hn_set_error(const char* fmt, ...);
 
 static inline int hn_cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// n / d for n < 2^31 as one multiply-high and a shift (d is fixed per launch; the constants are found on the host).
+// A 64-bit `/` or `%` by a runtime divisor is a ~100-instruction subroutine per call on the device.
+struct FastDiv { uint32_t d, mul, shr; };
+static inline FastDiv hn_fastdiv(uint32_t d) {
+  FastDiv f{d, 0u, 0u};
+  if (d > 1) {
+    uint32_t l = 0;
+    while ((1ull << l) < d) ++l;                     // ceil(log2 d)
+    f.mul = (uint32_t)(((1ull << (31 + l)) + d - 1) / d);
+    f.shr = l - 1;
+  }
+  return f;
+}
+
 // ---- device helpers ----------------------------------------------------------
+__device__ __forceinline__ uint32_t fd_div(uint32_t n, const FastDiv f) { return f.d == 1 ? n : __umulhi(n, f.mul) >> f.shr; }
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }

@@ -34,10 +34,66 @@ struct ScP {
   int HR, WR;                            // halo rows / cols
   int tiles_w, tiles_h, tiles;
   int nbuf;                              // halo buffers (2 unless they do not fit)
+  FastDiv fd_tw, fd_th;                  // tile index -> (b, th, tw) without runtime division
 };
 
+// tile -> image, tile row, tile column
+__device__ __forceinline__ void sc_tile(const ScP& p, int tile, int& b, int& th, int& tw) {
+  const uint32_t q = fd_div((uint32_t)tile, p.fd_tw);
+  tw = tile - (int)q * p.tiles_w;
+  const uint32_t bb = fd_div(q, p.fd_th);
+  th = (int)q - (int)bb * p.tiles_h;
+  b = (int)bb;
+}
+
+// Epilogue of one pass: bias, statistics, residual, activation, 4-byte stores (a warp store = 8 pixels x 16 bytes).
+// FAST (no residual, activation none / ReLU) and STATS are compile-time here and chosen by ONE warp-uniform branch per
+// pass: as run-time tests inside the unrolled (m-tile, row half, channel group) loops they cost a predicated-off copy of
+// the slow activation and the residual load per element (ncu: ~240 warp instructions per 8-pixel store at C = 8).
+// ytile / rtile: output / residual at the tile's first pixel; the per-store offset is 32-bit.
+template <int NT, int MT, bool FAST, bool STATS>
+__device__ __forceinline__ void sc_epilogue(const ScP& p, const float (&acc)[MT][NT][4], const float (&bia)[NT][2],
+                                            float (&csum)[NT][2], float (&csq)[NT][2], bf16* __restrict__ ytile,
+                                            const bf16* __restrict__ rtile, int pass, int warp, int g, int t) {
+  const bool relu = p.act == HN_ACT_RELU;
+  const int nlim = p.Cout - 2 * t;       // channel n = j * 8 + 2 t (+ 1) is real while j * 8 (+ 1) < nlim
+#pragma unroll
+  for (int i = 0; i < MT; ++i) {
+    const int mt = pass * MT + i;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int off = (warp * 2 + (mt >> 1)) * p.W + (mt & 1) * 16 + g + h * 8;
+      bf16* dst = ytile + (long long)off * p.ldy + 2 * t;
+      const bf16* rsd = (!FAST && rtile) ? rtile + (long long)off * p.ldr + 2 * t : nullptr;
+#pragma unroll
+      for (int j = 0; j < NT; ++j) {
+        float v0 = acc[i][j][h * 2] + bia[j][0], v1 = acc[i][j][h * 2 + 1] + bia[j][1];
+        if (STATS) {
+          const float r0 = bf16_round(v0), r1 = bf16_round(v1);
+          csum[j][0] += r0; csq[j][0] += r0 * r0;
+          csum[j][1] += r1; csq[j][1] += r1 * r1;
+        }
+        if (FAST) {
+          v0 = relu ? fmaxf(v0, 0.f) : v0;
+          v1 = relu ? fmaxf(v1, 0.f) : v1;
+        } else {
+          if (rsd) {
+            const float2 rr = __bfloat1622float2(*reinterpret_cast<const bf162*>(rsd + j * 8));
+            v0 += rr.x; v1 += rr.y;
+          }
+          v0 = apply_act(v0, p.act);
+          v1 = apply_act(v1, p.act);
+        }
+        v0 = j * 8 < nlim ? v0 : 0.f;
+        v1 = j * 8 + 1 < nlim ? v1 : 0.f;
+        *reinterpret_cast<uint32_t*>(dst + j * 8) = pack_bf16(v0, v1);
+      }
+    }
+  }
+}
+
 template <int NT>   // N/8 output-channel groups
-__global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
+__global__ void __launch_bounds__(SC_THREADS, NT == 1 ? 4 : (NT == 8 ? 1 : 2)) conv_sc_kernel(const ScP p) {
   constexpr int MT = NT == 8 ? 2 : 4;    // m-tiles (16 px) per pass, 4 per warp in total
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ float s_stat[2][NT * 8];
@@ -79,35 +135,62 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
 
   // halo of one tile -> buffer `buf` (cp.async, zero fill outside the image)
   const int halo_bytes = halo_chunks * 16;
+  const uint32_t sHa = smem_u32(sH), sZa = smem_u32(sZ), sWa = smem_u32(sW);
+  const bool one_src = !p.ups && p.CG1 == CG;      // one plain input: the common case gets the short address path
   auto stage_halo = [&](int tile, int buf) {
-    const int tw = tile % p.tiles_w, th = (tile / p.tiles_w) % p.tiles_h, b = tile / (p.tiles_w * p.tiles_h);
+    int tw, th, b;
+    sc_tile(p, tile, b, th, tw);
     const int h0 = th * TH, w0 = tw * TW;
-    uint8_t* dstb = sH + buf * halo_bytes;
     // one warp per halo row, lanes over the row's 16-byte chunks (no per-chunk division; the 64-bit row base once per row)
-    const uint32_t dsta = smem_u32(dstb);
+    const uint32_t dsta = sHa + (uint32_t)(buf * halo_bytes);
     for (int r = warp; r < p.HR; r += SC_THREADS / 32) {
       const int ih = h0 - p.pad + r;
       const bool rok = (unsigned)ih < (unsigned)p.H;
       const int srow = rok ? ih : 0;
       const long long rowpix = p.ups ? ((long long)b * (p.H >> 1) + (srow >> 1)) * (p.W >> 1) : ((long long)b * p.H + srow) * p.W;
       const uint32_t rowaddr = dsta + (uint32_t)(((r * p.WR) << p.lgCG) * 16);
-      for (int idx = lane; idx < (p.WR << p.lgCG); idx += 32) {
-        const int c = idx >> p.lgCG, c8 = idx & cgm;
-        const int iw = w0 - p.pad + c;
-        const bool ok = rok && (unsigned)iw < (unsigned)p.W;
-        const int sw_ = ok ? iw : 0;
-        const long long pix = rowpix + (p.ups ? (sw_ >> 1) : sw_);
-        const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
-        cp_async16(rowaddr + (uint32_t)(((c << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
+      if (one_src) {
+        const bf16* rowp = p.x1 + rowpix * p.ld1;
+        for (int idx = lane; idx < (p.WR << p.lgCG); idx += 32) {
+          const int c = idx >> p.lgCG, c8 = idx & cgm;
+          const int iw = w0 - p.pad + c;
+          const bool ok = rok && (unsigned)iw < (unsigned)p.W;
+          cp_async16(rowaddr + (uint32_t)(((c << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), rowp + (ok ? iw * p.ld1 + c8 * 8 : 0), ok);
+        }
+      } else {
+        for (int idx = lane; idx < (p.WR << p.lgCG); idx += 32) {
+          const int c = idx >> p.lgCG, c8 = idx & cgm;
+          const int iw = w0 - p.pad + c;
+          const bool ok = rok && (unsigned)iw < (unsigned)p.W;
+          const int sw_ = ok ? iw : 0;
+          const long long pix = rowpix + (p.ups ? (sw_ >> 1) : sw_);
+          const bf16* src = c8 < p.CG1 ? p.x1 + pix * p.ld1 + c8 * 8 : p.x2 + pix * p.ld2 + (c8 - p.CG1) * 8;
+          cp_async16(rowaddr + (uint32_t)(((c << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16), src, ok);
+        }
       }
     }
   };
+  // CG == 1 (8 input channels): one chunk per pixel, no swizzle, a k-step = two taps (lanes 0-15 / 16-31).  The tap offset
+  // of each k-step is a per-lane constant of the kernel: found once here instead of once per (k-step, m-tile, tile)
+  constexpr uint32_t NOKEY = 0xFFFFFFFFu;
+  uint32_t koff[5] = {NOKEY, NOKEY, NOKEY, NOKEY, NOKEY};     // Kc <= 9 chunks -> at most 5 k16 steps
+  if (CG == 1 && NT <= 2) {      // wider outputs keep the generic k-step loop below (register budget)
+#pragma unroll
+    for (int ks = 0; ks < 5; ++ks) {
+      const int gi = ks * 2 + (lane >> 4);
+      if (gi < p.Kc) {
+        const int kh = gi / p.KW, kw = gi - kh * p.KW;
+        koff[ks] = (uint32_t)(((kh * p.dil) * p.WR + kw * p.dil) * 16);
+      }
+    }
+  }
   // two halo buffers: the next tile streams in while this one is computed (keeps loads in flight)
   stage_halo(blockIdx.x, 0);
   cp_async_commit();
   int it = 0;
   for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
-    const int tw = tile % p.tiles_w, th = (tile / p.tiles_w) % p.tiles_h, b = tile / (p.tiles_w * p.tiles_h);
+    int tw, th, b;
+    sc_tile(p, tile, b, th, tw);
     const int h0 = th * TH, w0 = tw * TW;
     const int cur = p.nbuf == 2 ? (it & 1) : 0;
     if (p.nbuf == 2) {
@@ -118,7 +201,7 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
       cp_async_wait<0>();
     }
     __syncthreads();
-    const uint8_t* sHc = sH + cur * halo_bytes;
+    const uint32_t sHc = sHa + (uint32_t)(cur * halo_bytes);
 
 #pragma unroll
     for (int pass = 0; pass < 4 / MT; ++pass) {
@@ -144,7 +227,7 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
             const int mt = pass * MT + i;
             const int r = warp * 2 + (mt >> 1) + dr;
             const int c = (mt & 1) * 16 + (lane & 15) + dc;
-            abase[i] = smem_u32(sHc) + (uint32_t)(((r * p.WR + c) << p.lgCG) * 16);
+            abase[i] = sHc + (uint32_t)(((r * p.WR + c) << p.lgCG) * 16);
             akey[i] = (c >> p.sh) & cgm;
           }
           for (int kk = 0; kk < kpt; ++kk, ++ks) {
@@ -155,16 +238,48 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
                 const int row = j * 8 + (lane & 7) + ((lane >> 4) << 3);
                 const int ch = ks * 2 + ((lane >> 3) & 1);
                 ldsm_x4(bfr[j][0], bfr[j][1], bfr[j + 1 < NT ? j + 1 : j][0], bfr[j + 1 < NT ? j + 1 : j][1],
-                        smem_u32(sW + row * p.wrow + ch * 16));
+                        sWa + (uint32_t)(row * p.wrow + ch * 16));
               }
             } else {
-              ldsm_x2(bfr[0][0], bfr[0][1], smem_u32(sW + (lane & 7) * p.wrow + (ks * 2 + ((lane >> 3) & 1)) * 16));
+              ldsm_x2(bfr[0][0], bfr[0][1], sWa + (uint32_t)((lane & 7) * p.wrow + (ks * 2 + ((lane >> 3) & 1)) * 16));
             }
             const int c8 = kk * 2 + (lane >> 4);
             uint32_t af[MT][4];                               // all A fragments first: the MMAs then issue back to back
 #pragma unroll
             for (int i = 0; i < MT; ++i)
               ldsm_x4(af[i][0], af[i][1], af[i][2], af[i][3], abase[i] + (uint32_t)((c8 ^ akey[i]) << 4));
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+#pragma unroll
+              for (int j = 0; j < NT; ++j) mma_16816(acc[i][j], af[i], bfr[j][0], bfr[j][1]);
+          }
+        }
+      } else if (NT <= 2) {
+        uint32_t abase[MT];
+#pragma unroll
+        for (int i = 0; i < MT; ++i) {
+          const int mt = pass * MT + i;
+          abase[i] = sHc + (uint32_t)(((warp * 2 + (mt >> 1)) * p.WR + (mt & 1) * 16 + (lane & 15)) * 16);
+        }
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) {
+          if (ks < p.KS) {
+            uint32_t bfr[NT][2];
+            if (NT >= 2) {
+#pragma unroll
+              for (int j = 0; j < NT; j += 2) {
+                const int row = j * 8 + (lane & 7) + ((lane >> 4) << 3);
+                const int ch = ks * 2 + ((lane >> 3) & 1);
+                ldsm_x4(bfr[j][0], bfr[j][1], bfr[j + 1 < NT ? j + 1 : j][0], bfr[j + 1 < NT ? j + 1 : j][1],
+                        sWa + (uint32_t)(row * p.wrow + ch * 16));
+              }
+            } else {
+              ldsm_x2(bfr[0][0], bfr[0][1], sWa + (uint32_t)((lane & 7) * p.wrow + (ks * 2 + ((lane >> 3) & 1)) * 16));
+            }
+            uint32_t af[MT][4];
+#pragma unroll
+            for (int i = 0; i < MT; ++i)
+              ldsm_x4(af[i][0], af[i][1], af[i][2], af[i][3], koff[ks] != NOKEY ? abase[i] + koff[ks] : sZa);
 #pragma unroll
             for (int i = 0; i < MT; ++i)
 #pragma unroll
@@ -181,10 +296,10 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
             const int row = j * 8 + (lane & 7) + ((lane >> 4) << 3);
             const int ch = ks * 2 + ((lane >> 3) & 1);
             ldsm_x4(bfr[j][0], bfr[j][1], bfr[j + 1 < NT ? j + 1 : j][0], bfr[j + 1 < NT ? j + 1 : j][1],
-                    smem_u32(sW + row * p.wrow + ch * 16));
+                    sWa + (uint32_t)(row * p.wrow + ch * 16));
           }
         } else {
-          ldsm_x2(bfr[0][0], bfr[0][1], smem_u32(sW + (lane & 7) * p.wrow + (ks * 2 + ((lane >> 3) & 1)) * 16));
+          ldsm_x2(bfr[0][0], bfr[0][1], sWa + (uint32_t)((lane & 7) * p.wrow + (ks * 2 + ((lane >> 3) & 1)) * 16));
         }
         // A fragments: chunk gi of the K order = (tap, c8); lanes 0-15 first chunk, 16-31 second
         const int gi = ks * 2 + (lane >> 4);
@@ -197,42 +312,24 @@ __global__ void __launch_bounds__(SC_THREADS) conv_sc_kernel(const ScP p) {
           const int mt = pass * MT + i;
           const int r = warp * 2 + (mt >> 1) + dr;
           const int c = (mt & 1) * 16 + (lane & 15) + dc;
-          const uint32_t addr = kok ? smem_u32(sHc + (((r * p.WR + c) << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16) : smem_u32(sZ);
+          const uint32_t addr = kok ? sHc + (uint32_t)((((r * p.WR + c) << p.lgCG) + (c8 ^ ((c >> p.sh) & cgm))) * 16) : sZa;
           uint32_t af[4];
           ldsm_x4(af[0], af[1], af[2], af[3], addr);
 #pragma unroll
           for (int j = 0; j < NT; ++j) mma_16816(acc[i][j], af, bfr[j][0], bfr[j][1]);
         }
       }
-      // ---- epilogue of this pass ------------------------------------------------------------
-#pragma unroll
-      for (int i = 0; i < MT; ++i) {
-        const int mt = pass * MT + i;
-        const int oh = h0 + warp * 2 + (mt >> 1);
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int ow = w0 + (mt & 1) * 16 + g + h * 8;
-          const long long opix = ((long long)b * p.H + oh) * p.W + ow;
-          bf16* dst = p.y + opix * p.ldy;
-          const bf16* rsd = p.res ? p.res + opix * p.ldr : nullptr;
-#pragma unroll
-          for (int j = 0; j < NT; ++j) {
-            const int n = j * 8 + 2 * t;
-            float v0 = acc[i][j][h * 2] + bia[j][0], v1 = acc[i][j][h * 2 + 1] + bia[j][1];
-            if (p.ssum) {
-              const float r0 = bf16_round(v0), r1 = bf16_round(v1);
-              csum[j][0] += r0; csq[j][0] += r0 * r0;
-              csum[j][1] += r1; csq[j][1] += r1 * r1;
-            }
-            if (rsd) {
-              const float2 rr = __bfloat1622float2(*reinterpret_cast<const bf162*>(rsd + n));
-              v0 += rr.x; v1 += rr.y;
-            }
-            v0 = n < p.Cout ? apply_act(v0, p.act) : 0.f;
-            v1 = n + 1 < p.Cout ? apply_act(v1, p.act) : 0.f;
-            *reinterpret_cast<uint32_t*>(dst + n) = pack_bf16(v0, v1);
-          }
-        }
+      // ---- epilogue of this pass: one warp-uniform choice of the compiled variant ----------------
+      const long long tile_pix = ((long long)b * p.H + h0) * p.W + w0;
+      bf16* ytile = p.y + tile_pix * p.ldy;
+      const bf16* rtile = p.res ? p.res + tile_pix * p.ldr : nullptr;
+      const bool fast = p.act <= HN_ACT_RELU && !p.res;
+      if (fast) {
+        if (p.ssum) sc_epilogue<NT, MT, true, true>(p, acc, bia, csum, csq, ytile, rtile, pass, warp, g, t);
+        else sc_epilogue<NT, MT, true, false>(p, acc, bia, csum, csq, ytile, rtile, pass, warp, g, t);
+      } else {
+        if (p.ssum) sc_epilogue<NT, MT, false, true>(p, acc, bia, csum, csq, ytile, rtile, pass, warp, g, t);
+        else sc_epilogue<NT, MT, false, false>(p, acc, bia, csum, csq, ytile, rtile, pass, warp, g, t);
       }
     }
     __syncthreads();                                       // everyone is done reading this halo buffer
@@ -349,6 +446,7 @@ extern "C" int hn_conv_sc_fwd_res(const HnConv* d, const void* x1, const void* x
   p.wrow = wch * 16;
   p.HR = TH + (d->KH - 1) * d->dil; p.WR = TW + (d->KW - 1) * d->dil;
   p.tiles_w = d->W / TW; p.tiles_h = d->H / TH; p.tiles = d->B * p.tiles_w * p.tiles_h;
+  p.fd_tw = hn_fastdiv((uint32_t)p.tiles_w); p.fd_th = hn_fastdiv((uint32_t)p.tiles_h);
   const int n8 = (d->Cout + 7) / 8 * 8;
   const int NT = n8 <= 8 ? 1 : (n8 <= 16 ? 2 : (n8 <= 32 ? 4 : 8));
   p.nbuf = sc_smem_bytes(d, 2) <= 112 * 1024 ? 2 : 1;      // double-buffer when two CTAs per SM still fit
