@@ -262,6 +262,55 @@ def test_small_channel_conv_residual_and_upsample(ops, C, k):
     assert rel_l2(s.grad, sr) < BWD_TOL and rel_l2(w2.grad, wr) < BWD_TOL
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout,dil,ups", [
+    (3, 64, 96, 32, 32, 1, 0),      # 36 tiles, 9216 dW words: clusters of 8 CTAs (32 CTAs, four of them take two tiles)
+    (2, 128, 128, 16, 16, 2, 0),    # 64 tiles, double-buffered, clusters
+    (4, 128, 128, 8, 8, 3, 0),      # 128 tiles: plain grid (small flush), two tiles per CTA through both tile buffers
+    (2, 128, 128, 16, 32, 1, 1),    # upsample folded into the halo gather (general loader path), clusters
+    (6, 64, 64, 32, 64, 1, 0),      # Cout = 64: four 16-row blocks, 5 chunks per warp
+])
+def test_small_channel_weight_gradient_many_tiles(ops, B, H, W, Cin, Cout, dil, ups):
+    """hn_conv_wgrad_sc beyond one tile per CTA: the two tile buffers, the parked accumulator slices and the cluster
+    reduction through distributed shared memory (launches whose grid x dW size reaches 1e5 atomics) against torch's
+    conv weight gradient; bias gradient and input gradient ride along."""
+    import contextlib
+    from hybridnet import _lib
+    h, w_ = (H // 2, W // 2) if ups else (H, W)
+    x = _rand(B, Cin, h, w_, seed=21).requires_grad_(True)
+    w = _rand(Cout, Cin, 3, 3, seed=22, scale=1.0 / math.sqrt(Cin * 9)).requires_grad_(True)
+    b = _rand(Cout, seed=23, scale=0.1).requires_grad_(True)
+    xin = F.interpolate(x, scale_factor=2.0, mode="nearest") if ups else x
+    ref = F.conv2d(xin, w, b, 1, dil, dil)
+    gy = _rand(*ref.shape, seed=24)
+    ref.backward(gy)
+    want = [t.grad.clone() for t in (x, w, b)]
+    for t in (x, w, b):
+        t.grad = None
+    names = []
+
+    @contextlib.contextmanager
+    def record(name, args):
+        names.append(name)
+        yield
+    _lib.set_profiler(record)
+    try:
+        out = ops.to_nchw(ops.conv2d(ops.to_nhwc(x), w, b, pad=dil, dil=dil, ups=ups), Cout)
+        assert rel_l2(out, ref) < FWD_TOL
+        out.backward(gy)
+    finally:
+        _lib.set_profiler(None)
+    assert "hn_conv_wgrad_sc" in names and "hn_conv2d_wgrad" not in names, names
+    for t, r in zip((x, w, b), want):
+        assert rel_l2(t.grad, r) < BWD_TOL
+    # twice the same launch: the second accumulates onto the first (fp32 atomics: order differs, values agree)
+    g1 = w.grad.clone()
+    w.grad = None
+    x.grad = None
+    b.grad = None
+    ops.to_nchw(ops.conv2d(ops.to_nhwc(x), w, b, pad=dil, dil=dil, ups=ups), Cout).backward(gy)
+    assert rel_l2(w.grad, g1) < 1e-5
+
+
 @pytest.mark.parametrize("cin,cout", [(64, 32), (512, 256), (256, 384)])
 def test_conv_transpose_k2s2(ops, cin, cout):
     B, H = 2, 8
