@@ -613,17 +613,19 @@ def deferred_side_stream():
     return _deferred["side"]
 
 
-def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw):
-    """dz: gradient at the conv output (NHWC, padded channels zero). Returns dx1, dx2, dW."""
+def _conv_backward(g, x1, x2, weight, dz, need_dx, need_dw, bias=None):
+    """dz: gradient at the conv output (NHWC, padded channels zero). Returns dx1, dx2, dW.
+    bias: (sink slice, parameter address) of an activation-free conv's bias whose gradient (column sums of dz) is still
+    owed: the sums are then taken beside the weight gradient (on the side stream when there is one)."""
     if not (WGRAD_OVERLAP and need_dx and need_dw):
-        return _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, None)
+        return _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, None, bias)
     dz, _ = nhwc(dz)
-    return _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, _side_stream(dz.device))
+    return _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, _side_stream(dz.device), bias)
 
 
-def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side):
+def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side, bias=None):
     dx1 = dx2 = dw = None
-    dz, _ = nhwc(dz)
+    dz, lddz = nhwc(dz)
     B = x1.shape[0]
     C1 = x1.shape[3]
     C2 = x2.shape[3] if x2 is not None else 0
@@ -632,6 +634,9 @@ def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side):
     if side is not None:
         side.wait_stream(main)
     with (torch.cuda.stream(side) if side is not None else contextlib.nullcontext()):
+        if bias is not None:
+            call("hn_colsum", dz.data_ptr(), dz.shape[0] * dz.shape[1] * dz.shape[2], dz.shape[3], lddz,
+                 bias[0].data_ptr(), _stream())
         if need_dw:
             sunk = _sink_for(weight)
             dw = sunk.view(weight.shape) if sunk is not None else _f32(tuple(weight.shape), weight)
@@ -676,6 +681,8 @@ def _conv_backward_on(g, x1, x2, weight, dz, need_dx, need_dw, side):
     if side is not None:
         if not (sunk is not None and WGRAD_DEFER and _defer_join(main, side, (dz, x1, x2))):
             main.wait_stream(side)
+    if bias is not None:
+        _sink_done(bias[1])
     if sunk is not None:
         _sink_done(weight.data_ptr())
         dw = None
@@ -703,8 +710,18 @@ class _ConvFn(torch.autograd.Function):
         x1, x2, weight, y = ctx.saved_tensors
         g = ctx.g
         need = ctx.needs_input_grad
-        dz, dbias = _act_bwd(dy, y, ctx.act, ctx.has_bias and need[3], ctx.bias)
-        dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2])
+        want_db = ctx.has_bias and need[3]
+        late_bias = None
+        if (want_db and ctx.act == ACT_NONE and need[2] and ctx.bias.dtype == torch.float32
+                and ctx.bias.numel() == dy.shape[3]):
+            # activation-free conv: dz = dy and the bias gradient is one column-sum launch.  With a slice in the gradient
+            # sink it goes beside the weight gradient (the side stream under WGRAD_OVERLAP) instead of ahead of the input
+            # gradient on this stream
+            bs = _sink_for(ctx.bias)
+            if bs is not None:
+                late_bias, want_db = (bs, ctx.bias.data_ptr()), False
+        dz, dbias = _act_bwd(dy, y, ctx.act, want_db, ctx.bias)
+        dx1, dx2, dw = _conv_backward(g, x1, x2, weight, dz, need[0] or need[1], need[2], late_bias)
         if dbias is not None:
             dbias = dbias[: g.Cout]
         return (dx1 if need[0] else None, dx2 if need[1] else None, dw, dbias,
