@@ -19,10 +19,14 @@ timeout -k 10 200 python scripts/attn_bench.py --tc 3 --tcbwd > $O/attn_bench_tc
 (timeout -k 10 200 python scripts/conv_bench.py; timeout -k 10 200 python scripts/conv_bench.py --wgrad) > $O/conv_bench.txt 2>&1
 timeout -k 10 200 python scripts/bn_bench.py > $O/bn_bench.txt 2>&1
 [ -x scripts/build/umma_bench ] && scripts/build/umma_bench > $O/umma_bench.txt 2>&1
-# launch list of the default command (cold-cache, serialised: shares, not absolutes), only after it ran clean above
-timeout -k 10 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1400 --csv \
-  --log-file $O/ncu_launches_fct.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extra > $O/ncu.log 2>&1
-python scripts/ncu_launches.py $O/ncu_launches_fct.csv "FCT B=32: first 1400 launches of bench.py --steps 1 --warmup 3 --no-extra (about 2.5 steps)" > $O/ncu_launches_fct_summary.txt 2>&1
+(timeout -k 10 200 python scripts/conv_bench.py --graph --only fct_; timeout -k 10 200 python scripts/conv_bench.py --wgrad --graph --only fct_,un_3x3_32; timeout -k 10 100 python scripts/dwln_bench.py) > $O/small_channel_bench.txt 2>&1
+# launch list of the default command (cold-cache, serialised: shares, not absolutes), only after it ran clean above.
+# About six GPU-minutes under ncu: NCU_LIST=1 to include it.
+if [ "${NCU_LIST:-0}" = 1 ]; then
+  timeout -k 10 700 ncu --metrics gpu__time_duration.sum --clock-control none -c 2600 --csv \
+    --log-file $O/ncu_launches_fct.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extra > $O/ncu.log 2>&1
+  python scripts/ncu_launches.py $O/ncu_launches_fct.csv "FCT B=32, bench.py --steps 1 --warmup 3 --no-extra: exactly one step (between two adamw_kernel launches)" --step adamw > $O/ncu_launches_fct_summary.txt 2>&1
+fi
 # roofline.traffic: the dominant kernel of each workload at the bench shapes
 timeout -k 10 300 ncu --set full --clock-control none -k regex:attn_bwd_tc_kernel -c 1 -o $O/attn_bwd_d4 python scripts/ncu_attn.py 4 tc 32 16384 > $O/ncu_attn4.log 2>&1
 timeout -k 10 300 ncu --set full --clock-control none -k regex:attn_bwd_tc_kernel -c 1 -o $O/attn_bwd_d8 python scripts/ncu_attn.py 8 tc 32 4096 > $O/ncu_attn8.log 2>&1
