@@ -311,7 +311,7 @@ class CapturedStep:
         if self._down is None:
             dev = self.x.device
             self._down = torch.cuda.Stream(device=dev)
-            self._out_stage = [torch.empty_like(self.loss) for _ in range(2)]
+            self._out_stage = [torch.empty_like(self.loss.detach()) for _ in range(2)]
             self._out_host = [torch.empty(self.loss.shape, dtype=self.loss.dtype).pin_memory() for _ in range(2)]
             self._out_ready = [torch.cuda.Event() for _ in range(2)]
             self._out_done = [torch.cuda.Event() for _ in range(2)]
@@ -320,9 +320,10 @@ class CapturedStep:
         self._j ^= 1
         cur = torch.cuda.current_stream()
         cur.wait_event(self._out_done[j])             # the copy that last read this staging buffer is over
-        self._out_stage[j].copy_(self.loss, non_blocking=True)
+        with torch.no_grad():                         # (a training step's loss requires grad: the copies must not record)
+            self._out_stage[j].copy_(self.loss.detach(), non_blocking=True)
         self._out_ready[j].record(cur)
-        with torch.cuda.stream(self._down):
+        with torch.cuda.stream(self._down), torch.no_grad():
             self._down.wait_event(self._out_ready[j])
             self._out_host[j].copy_(self._out_stage[j], non_blocking=True)
             self._out_done[j].record(self._down)
