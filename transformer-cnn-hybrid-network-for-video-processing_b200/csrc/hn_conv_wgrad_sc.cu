@@ -7,7 +7,8 @@
 // columns, the 32 pixel k-steps of a tile to KSPLIT warp rows; every warp keeps its slice of dW in
 // registers across all tiles of the CTA; at the end every warp parks its slice in shared memory (fragment order, its own
 // region: no shared atomics), the KSPLIT slices of an element are summed by one thread and flushed with one fp32 global
-// atomic per element per CTA.  Two tile buffers when they fit beside a second CTA: the next tile streams in while this
+// atomic per element per CTA -- or, launched as thread-block clusters of 8 CTAs, per element per CLUSTER: the CTAs first sum
+// their dW through distributed shared memory (see the end of the kernel).  Two tile buffers when they fit beside a second CTA: the next tile streams in while this
 // one is contracted (single-buffered, the loads of every tile were fully exposed: 3.5 tiles per CTA, ~6 us each at C = 8).
 #include "hn_common.cuh"
 
@@ -66,7 +67,6 @@ __global__ void __launch_bounds__(WS_THREADS, 2) wgrad_sc_kernel(const WsP p) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int s_tap[9];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = lane >> 2, t = lane & 3;
   const int CG = p.CG, cgm = CG - 1, NC = p.NC, ncm = NC - 1;
   const int halo_chunks = p.HR * p.WR * CG;
   uint8_t* sH = smem;
