@@ -179,7 +179,8 @@ __global__ void __launch_bounds__(SC_THREADS, NT == 1 ? 4 : (NT == 8 ? 1 : 2)) c
     for (int ks = 0; ks < 5; ++ks) {
       const int gi = ks * 2 + (lane >> 4);
       if (gi < p.Kc) {
-        const int kh = gi / p.KW, kw = gi - kh * p.KW;
+        const int kh = p.KW == 3 ? (gi * 11) >> 5 : 0;       // gi / 3 for gi < 10 (KW is 1 or 3 here: sc_ok); no run-time division
+        const int kw = gi - kh * p.KW;
         koff[ks] = (uint32_t)(((kh * p.dil) * p.WR + kw * p.dil) * 16);
       }
     }

@@ -22,6 +22,9 @@ constexpr int WS_THREADS = 256;
 #ifndef WS_CLUSTER_MIN_FLUSH
 #define WS_CLUSTER_MIN_FLUSH 100000   // cluster launches only when grid x dW elements reaches this many global atomics
 #endif
+#ifndef WS_MINB
+#define WS_MINB(MTN) 2   // resident CTAs per SM the register allocation is held to (3 for the 16-row kernels measured no gain: 109 -> 124 us at 64 -> 8 channels)
+#endif
 #ifndef WS_MIN_TILES
 #define WS_MIN_TILES 2     // tiles per CTA the grid is sized for
 #endif
@@ -63,7 +66,7 @@ __device__ __forceinline__ float ld_dsmem(uint32_t addr) {
 }
 
 template <int MTN, int CPW>   // 16-row blocks of Cout, column chunks per warp
-__global__ void __launch_bounds__(WS_THREADS, 2) wgrad_sc_kernel(const WsP p) {
+__global__ void __launch_bounds__(WS_THREADS, WS_MINB(MTN)) wgrad_sc_kernel(const WsP p) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int s_tap[9];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
