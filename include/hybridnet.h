@@ -298,7 +298,9 @@ int hn_conv_sc_fwd_res(const HnConv* d, const void* x1, const void* x2, const vo
                        const float* bias, const void* res, void* y, float* stat_sum,
                        float* stat_sqsum, void* stream);
 
-/* small-channel weight gradient: same contract as hn_conv2d_wgrad for the hn_conv_sc_fwd geometries */
+/* small-channel weight gradient: same contract as hn_conv2d_wgrad for the hn_conv_sc_fwd geometries (dw is accumulated
+ * into with fp32 atomics: zero it first).  Large flushes are launched as thread-block clusters of 8 CTAs that sum dW
+ * through distributed shared memory before the atomics; graph capturable, allocates nothing. */
 int hn_conv_wgrad_sc_supported(const HnConv* d);
 int hn_conv_wgrad_sc(const HnConv* d, const void* x1, const void* x2, const void* dy, float* dw,
                      int Creal, long long s_n, long long s_c, long long s_kh, long long s_kw,
