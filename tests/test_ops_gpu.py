@@ -447,10 +447,10 @@ def test_maxpool_dropout_add_gelu3_layernorm(ops):
             assert rel_l2(t.grad, r) < BWD_TOL
 
 
-@pytest.mark.parametrize("C", [8, 16, 32, 64, 128])
-def test_dwconv_relu_ln_qkv(ops, C):
-    B, H = 2, 12
-    x = _rand(B, C, H, H, seed=1).requires_grad_(True)
+@pytest.mark.parametrize("C,B,H,W", [(8, 2, 12, 12), (16, 2, 12, 12), (32, 2, 12, 12), (64, 2, 12, 12), (128, 2, 12, 12),
+                                     (8, 4, 40, 72), (32, 3, 20, 36)])      # several grid-stride rounds, H != W, no power of two
+def test_dwconv_relu_ln_qkv(ops, C, B, H, W):
+    x = _rand(B, C, H, W, seed=1).requires_grad_(True)
     # the reference's twelve separate parameter tensors: conv_{q,k,v}.weight [C,1,3,3] / .bias, layernorm_{q,k,v}.weight / .bias
     w = [_rand(C, 1, 3, 3, seed=20 + t, scale=0.4).requires_grad_(True) for t in range(3)]
     b = [_rand(C, seed=30 + t, scale=0.2).requires_grad_(True) for t in range(3)]
