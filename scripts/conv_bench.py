@@ -44,12 +44,15 @@ def main():
     ap.add_argument("--wgrad", action="store_true")
     ap.add_argument("--nostats", action="store_true")
     ap.add_argument("--graph", action="store_true", help="time the launches inside one CUDA graph")
+    ap.add_argument("--nosc", action="store_true", help="skip the small-channel kernels (what the other paths make of the same layer)")
     ap.add_argument("--lib", default="", help="a variant library built by scripts/attn_variants.sh")
     a = ap.parse_args()
     if a.lib:
         _lib.LIB_PATH = os.path.abspath(a.lib)
         print("library:", a.lib)
     lib = _lib.load()
+    if a.nosc:
+        ops.USE_SC = False
     dev = torch.device("cuda")
     torch.manual_seed(0)
     print(f"{'geometry':22s} {'kernel':18s} {'us':>9s} {'TFLOP/s':>9s} {'GB/s':>8s}")
